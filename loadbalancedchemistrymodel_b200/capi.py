@@ -1,0 +1,176 @@
+"""ctypes binding of the C ABI in ``include/lbchem.h`` (the product library ``liblbchem.so``).
+
+The library is hand-written CUDA for sm_100a plus a C++ host layer; there is no CPU fallback: if the
+shared object is missing or a CUDA device is absent, calls fail loudly.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+from .foam_io import Mechanism
+
+_HERE = Path(__file__).resolve().parent
+LIB_PATH = _HERE / "csrc" / "liblbchem.so"
+
+SOLVER_NONE, SOLVER_EULER_IMPLICIT, SOLVER_ROSENBROCK34, SOLVER_SEULEX = 0, 1, 2, 3
+SOLVERS = {
+    "noChemistrySolver": SOLVER_NONE,
+    "EulerImplicit": SOLVER_EULER_IMPLICIT,
+    "Rosenbrock34": SOLVER_ROSENBROCK34,
+    "seulex": SOLVER_SEULEX,
+}
+CELL_OK, CELL_SKIPPED, CELL_MAX_STEPS, CELL_UNDERFLOW, CELL_SINGULAR, CELL_NAN = range(6)
+
+_dp = C.POINTER(C.c_double)
+_ip = C.POINTER(C.c_int32)
+
+
+class MechDesc(C.Structure):
+    _fields_ = [
+        ("n_species", C.c_int32), ("n_reactions", C.c_int32), ("n_eff", C.c_int32), ("reserved", C.c_int32),
+        ("W", _dp), ("Tlow", _dp), ("Thigh", _dp), ("Tcommon", _dp), ("janaf_high", _dp), ("janaf_low", _dp),
+        ("rtype", _ip), ("reversible", _ip), ("arr", _dp), ("arr0", _dp), ("troe", _dp),
+        ("eff_index", _ip), ("eff", _dp),
+        ("lhs_ptr", _ip), ("lhs_species", _ip), ("lhs_nu", _dp), ("lhs_exp", _dp),
+        ("rhs_ptr", _ip), ("rhs_species", _ip), ("rhs_nu", _dp), ("rhs_exp", _dp),
+    ]
+
+
+class Options(C.Structure):
+    _fields_ = [
+        ("solver", C.c_int32), ("max_steps", C.c_int32), ("abs_tol", C.c_double), ("rel_tol", C.c_double),
+        ("Treact", C.c_double), ("deltaTChemMax", C.c_double), ("cTauChem", C.c_double),
+        ("eq_rate_limiter", C.c_int32), ("dfdx_is_dcdt", C.c_int32), ("gas_constant", C.c_double),
+        ("kc_floor", C.c_double), ("threads_per_cell", C.c_int32), ("sort_by_cost", C.c_int32),
+    ]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n_cells", C.c_int64), ("n_steps", C.c_int64), ("n_attempts", C.c_int64), ("n_jac", C.c_int64),
+        ("n_lu", C.c_int64), ("n_solve", C.c_int64), ("n_rhs", C.c_int64), ("n_failed", C.c_int64),
+        ("kernel_ms", C.c_double), ("kernel_launches", C.c_int32), ("reserved", C.c_int32),
+    ]
+
+
+# OpenFOAM v2306 thermodynamic::RR = 1e3 * NA * k (etc/controlDict DimensionedConstants, SI set)
+RR_DEFAULT = 1e3 * (6.0221417930e23 * 1.3806504e-23)
+
+
+def default_options(**kw) -> Options:
+    """OpenFOAM defaults (ODESolver: absTol SMALL, relTol 1e-4, maxSteps 10000; Treact 0; deltaTChemMax GREAT)."""
+    o = Options(
+        solver=SOLVER_ROSENBROCK34, max_steps=10000, abs_tol=1e-15, rel_tol=1e-4, Treact=0.0,
+        deltaTChemMax=1e15, cTauChem=1.0, eq_rate_limiter=0, dfdx_is_dcdt=1, gas_constant=RR_DEFAULT,
+        kc_floor=1e-6, threads_per_cell=0, sort_by_cost=0,
+    )
+    for k, v in kw.items():
+        if k == "solver" and isinstance(v, str):
+            v = SOLVERS[v]
+        if not hasattr(o, k):
+            raise AttributeError(k)
+        setattr(o, k, v)
+    return o
+
+
+class MechArrays:
+    """Keeps contiguous numpy copies alive and exposes them as a ``lbchem_mech_desc``."""
+
+    def __init__(self, mech: Mechanism):
+        self.mech = mech
+        self._keep = {}
+        d = MechDesc()
+        d.n_species, d.n_reactions, d.n_eff = mech.n_species, mech.n_reactions, int(mech.eff.shape[0])
+        for name, typ in MechDesc._fields_[4:]:
+            arr = getattr(mech, name)
+            if typ is _dp:
+                a = np.ascontiguousarray(arr, dtype=np.float64)
+                if a.size == 0:
+                    a = np.zeros(1)
+                ptr = a.ctypes.data_as(_dp)
+            else:
+                a = np.ascontiguousarray(arr, dtype=np.int32)
+                if a.size == 0:
+                    a = np.zeros(1, np.int32)
+                ptr = a.ctypes.data_as(_ip)
+            self._keep[name] = a
+            setattr(d, name, ptr)
+        self.desc = d
+
+
+def _as_dp(a):
+    return None if a is None else a.ctypes.data_as(_dp)
+
+
+def _as_ip(a):
+    return None if a is None else a.ctypes.data_as(_ip)
+
+
+_lib = None
+
+
+def load_library(path: Path | None = None) -> C.CDLL:
+    """dlopen liblbchem.so and declare prototypes. Raises if the CUDA library has not been built."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    p = Path(path) if path else LIB_PATH
+    if not p.exists():
+        raise RuntimeError(
+            f"{p} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU fallback for the chemistry path)"
+        )
+    lib = C.CDLL(str(p))
+    H = C.c_void_p
+    lib.lbchem_version.restype = C.c_char_p
+    lib.lbchem_default_options.argtypes = [C.POINTER(Options)]
+    lib.lbchem_create.argtypes = [C.POINTER(MechDesc), C.c_int, C.POINTER(H)]
+    lib.lbchem_destroy.argtypes = [H]
+    lib.lbchem_set_options.argtypes = [H, C.POINTER(Options)]
+    lib.lbchem_get_options.argtypes = [H, C.POINTER(Options)]
+    lib.lbchem_last_error.argtypes = [H]
+    lib.lbchem_last_error.restype = C.c_char_p
+    sig = [H, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double,
+           C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.lbchem_solve_batch.argtypes = sig + [C.c_void_p]
+    lib.lbchem_solve_batch_host.argtypes = sig
+    lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
+    lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
+    lib.lbchem_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
+    lib.lbchem_cells_to_send.restype = C.c_int32
+    if path is None:
+        _lib = lib
+    return lib
+
+
+EXPORTED_SYMBOLS = (
+    "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
+    "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
+    "lbchem_cells_to_send"
+).split()
+
+
+def balance_plan(cost, cells=None, min_fraction=0.02, tdac=False, lib=None):
+    """``updateProcessorBalancing`` for every rank. Returns (send, recv): send[r] = [(to, frac), ...]."""
+    lib = lib or load_library()
+    cost = np.ascontiguousarray(cost, dtype=np.float64)
+    P = cost.shape[0]
+    cells = np.zeros(P, np.int32) if cells is None else np.ascontiguousarray(cells, dtype=np.int32)
+    sp = np.zeros(P + 1, np.int32); rp = np.zeros(P + 1, np.int32)
+    st = np.zeros(P * P, np.int32); sf = np.zeros(P * P); rf = np.zeros(P * P, np.int32)
+    rc = lib.lbchem_balance_plan(P, _as_dp(cost), _as_ip(cells), float(min_fraction), int(bool(tdac)),
+                                 _as_ip(sp), _as_ip(st), _as_dp(sf), _as_ip(rp), _as_ip(rf))
+    if rc != 0:
+        raise RuntimeError(f"lbchem_balance_plan failed: {rc}")
+    send = [[(int(st[k]), float(sf[k])) for k in range(sp[r], sp[r + 1])] for r in range(P)]
+    recv = [[int(rf[k]) for k in range(rp[r], rp[r + 1])] for r in range(P)]
+    return send, recv
+
+
+def cells_to_send(cell_cost, target, start=0, lib=None) -> int:
+    lib = lib or load_library()
+    cell_cost = np.ascontiguousarray(cell_cost, dtype=np.float64)
+    return int(lib.lbchem_cells_to_send(_as_dp(cell_cost), cell_cost.shape[0], float(target), int(start)))
