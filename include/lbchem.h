@@ -174,6 +174,19 @@ int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy,
 int lbchem_get_stats(lbchem_handle h, lbchem_stats* out);
 
 /*
+ * Test hook: evaluate one building block of the integrator for nItems states on the device, with the
+ * same device functions lbchem_solve_batch uses (so a parity failure can be localised). HOST pointers;
+ * strides in doubles. With n = n_species + 2 and y = (c[0..nSp), T, p):
+ *   LBCHEM_PROBE_DERIV   in y[n]               out dydt[n]           StandardChemistryModel::derivatives
+ *   LBCHEM_PROBE_JAC     in y[n]               out dfdx[n], J[n*n]   StandardChemistryModel::jacobian
+ *   LBCHEM_PROBE_LUSOLVE in A[n*n], b[n]       out x[n]              LUDecompose + LUBacksubstitute
+ *   LBCHEM_PROBE_RATES   in y[n]               out kf[nR], kr[nR]    Reaction::kf / kr
+ */
+enum { LBCHEM_PROBE_DERIV = 0, LBCHEM_PROBE_JAC = 1, LBCHEM_PROBE_LUSOLVE = 2, LBCHEM_PROBE_RATES = 3 };
+int lbchem_probe(lbchem_handle h, int32_t kind, int32_t n_items, const double* in, int32_t in_stride,
+                 double* out, int32_t out_stride);
+
+/*
  * The balancing plan (bit-exact with the reference for the same cost vector).
  *   cost[nranks], cells[nranks]: all-gathered per-rank total cost and cell count.
  * Outputs are the plan of every rank, flattened in push order:

@@ -138,6 +138,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_solve_batch.argtypes = sig + [C.c_void_p]
     lib.lbchem_solve_batch_host.argtypes = sig
     lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
+    lib.lbchem_probe.argtypes = [H, C.c_int32, C.c_int32, _dp, C.c_int32, _dp, C.c_int32]
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
     lib.lbchem_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
     lib.lbchem_cells_to_send.restype = C.c_int32
@@ -149,7 +150,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send"
+    "lbchem_cells_to_send lbchem_probe"
 ).split()
 
 
@@ -174,3 +175,103 @@ def cells_to_send(cell_cost, target, start=0, lib=None) -> int:
     lib = lib or load_library()
     cell_cost = np.ascontiguousarray(cell_cost, dtype=np.float64)
     return int(lib.lbchem_cells_to_send(_as_dp(cell_cost), cell_cost.shape[0], float(target), int(start)))
+
+
+PROBE_DERIV, PROBE_JAC, PROBE_LUSOLVE, PROBE_RATES = 0, 1, 2, 3
+
+
+class Chemistry:
+    """Owner of one ``lbchem_handle``: a mechanism bound to one CUDA device (one per rank / host thread).
+
+    Mirrors what the reference model object holds after construction
+    (``LoadBalancedChemistryModel.C:32-59``): the mechanism, the solver options and scratch.
+    """
+
+    def __init__(self, mech: Mechanism, options: Options | None = None, device: int = -1, lib=None):
+        self.lib = lib or load_library()
+        self.mech = mech
+        self.arrays = MechArrays(mech)
+        self.h = C.c_void_p()
+        rc = self.lib.lbchem_create(C.byref(self.arrays.desc), int(device), C.byref(self.h))
+        if rc != 0:
+            msg = self.lib.lbchem_last_error(self.h).decode() if self.h else "no CUDA device"
+            if self.h:
+                self.lib.lbchem_destroy(self.h)
+                self.h = C.c_void_p()
+            raise RuntimeError(f"lbchem_create failed ({rc}): {msg}")
+        self.options = options or default_options()
+        self.set_options(self.options)
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.lbchem_destroy(self.h)
+            self.h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise RuntimeError(f"{what} failed ({rc}): {self.lib.lbchem_last_error(self.h).decode()}")
+
+    def set_options(self, options: Options):
+        self._check(self.lib.lbchem_set_options(self.h, C.byref(options)), "lbchem_set_options")
+        self.options = options
+
+    def stats(self) -> dict:
+        st = Stats()
+        self._check(self.lib.lbchem_get_stats(self.h, C.byref(st)), "lbchem_get_stats")
+        return {k: getattr(st, k) for k, _ in Stats._fields_ if k != "reserved"}
+
+    # ---- host buffers (numpy) -------------------------------------------------------------
+    def solve_host(self, Y, T, p, rho, deltaT, deltaTChem, out=None):
+        """Y [nSp, n] field-major float64 numpy arrays; returns dict(RR, T, deltaTChem, cost, status)."""
+        Y = np.ascontiguousarray(Y, dtype=np.float64)
+        nSp, n = Y.shape
+        T = np.ascontiguousarray(T, dtype=np.float64)
+        p = np.ascontiguousarray(np.broadcast_to(p, (n,)), dtype=np.float64)
+        rho = np.ascontiguousarray(rho, dtype=np.float64)
+        if out is not None and "deltaTChem" in out:
+            dtc = out["deltaTChem"]; dtc[...] = deltaTChem
+        else:
+            dtc = np.array(np.broadcast_to(deltaTChem, (n,)), dtype=np.float64)
+        if np.ndim(deltaT) == 0:
+            dT_arr, dT_u = None, float(deltaT)
+        else:
+            dT_arr, dT_u = np.ascontiguousarray(deltaT, dtype=np.float64), 0.0
+        o = out or {}
+        RR = o.get("RR") if o.get("RR") is not None else np.empty_like(Y)
+        Tout = o.get("T") if o.get("T") is not None else np.empty(n)
+        cost = o.get("cost") if o.get("cost") is not None else np.empty(n)
+        status = o.get("status") if o.get("status") is not None else np.empty(n, np.int32)
+        vp = lambda a: None if a is None else C.c_void_p(a.ctypes.data)
+        rc = self.lib.lbchem_solve_batch_host(self.h, n, n, vp(Y), vp(T), vp(p), vp(rho), vp(dT_arr), dT_u,
+                                              vp(dtc), vp(RR), vp(Tout), vp(cost), vp(status))
+        self._check(rc, "lbchem_solve_batch_host")
+        return dict(RR=RR, T=Tout, deltaTChem=dtc, cost=cost, status=status)
+
+    # ---- device buffers (anything with data_ptr(): torch CUDA tensors) ----------------------
+    def solve_device(self, n, ldy, Y, T, p, rho, deltaT, deltaTChem, RR, Tout=None, cost=None, status=None, stream=0):
+        ptr = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        if isinstance(deltaT, (int, float)):
+            dT_arr, dT_u = None, float(deltaT)
+        else:
+            dT_arr, dT_u = deltaT, 0.0
+        rc = self.lib.lbchem_solve_batch(self.h, int(n), int(ldy), ptr(Y), ptr(T), ptr(p), ptr(rho), ptr(dT_arr), dT_u,
+                                         ptr(deltaTChem), ptr(RR), ptr(Tout), ptr(cost), ptr(status),
+                                         C.c_void_p(int(stream)))
+        self._check(rc, "lbchem_solve_batch")
+
+    def probe(self, kind, x):
+        """x [nItems, inStride] -> out [nItems, outStride] (see include/lbchem.h: lbchem_probe)."""
+        x = np.ascontiguousarray(x, dtype=np.float64)
+        n = self.mech.n_species + 2
+        nR = self.mech.n_reactions
+        out_w = {PROBE_DERIV: n, PROBE_JAC: n + n * n, PROBE_LUSOLVE: n, PROBE_RATES: 2 * nR}[kind]
+        out = np.zeros((x.shape[0], out_w))
+        self._check(self.lib.lbchem_probe(self.h, kind, x.shape[0], _as_dp(x), x.shape[1], _as_dp(out), out_w),
+                    "lbchem_probe")
+        return out
