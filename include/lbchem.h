@@ -187,6 +187,12 @@ int lbchem_probe(lbchem_handle h, int32_t kind, int32_t n_items, const double* i
                  double* out, int32_t out_stride);
 
 /*
+ * FP64-pipe peak of the device (DFMA micro-benchmark, ~ms_target milliseconds): the roofline denominator of
+ * the chemistry kernels (bench.py; MEASURED_PEAKS.json carries no FP64 figure). device < 0: current device.
+ */
+int lbchem_fp64_peak(int device, double ms_target, double* tflops, double* sm_count);
+
+/*
  * The balancing plan (bit-exact with the reference for the same cost vector).
  *   cost[nranks], cells[nranks]: all-gathered per-rank total cost and cell count.
  * Outputs are the plan of every rank, flattened in push order:

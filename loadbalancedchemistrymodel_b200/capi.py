@@ -139,6 +139,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_solve_batch_host.argtypes = sig
     lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
     lib.lbchem_probe.argtypes = [H, C.c_int32, C.c_int32, _dp, C.c_int32, _dp, C.c_int32]
+    lib.lbchem_fp64_peak.argtypes = [C.c_int, C.c_double, _dp, _dp]
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
     lib.lbchem_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
     lib.lbchem_cells_to_send.restype = C.c_int32
@@ -150,7 +151,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_probe"
+    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak"
 ).split()
 
 
@@ -275,3 +276,13 @@ class Chemistry:
         self._check(self.lib.lbchem_probe(self.h, kind, x.shape[0], _as_dp(x), x.shape[1], _as_dp(out), out_w),
                     "lbchem_probe")
         return out
+
+
+def fp64_peak(device: int = -1, ms_target: float = 200.0, lib=None) -> float:
+    """Measured DFMA rate of the device in TFLOP/s (lbchem_fp64_peak)."""
+    lib = lib or load_library()
+    t = C.c_double(); s = C.c_double()
+    rc = lib.lbchem_fp64_peak(int(device), float(ms_target), C.byref(t), C.byref(s))
+    if rc != 0:
+        raise RuntimeError(f"lbchem_fp64_peak failed: {rc}")
+    return t.value
