@@ -1,0 +1,305 @@
+#!/usr/bin/env python
+"""bench.py — cell-chemistry solves/s for one flow step (BASELINE.json metric).
+
+Workload at every N: BASELINE config 3, "GRI-Mech 3.0 (53 species, 325 reactions), 1M synthetic cells,
+uniform cost" per GPU (weak scaling: cells are independent, shards carry no data-path collective; the only
+exchange is the reference's all-gather of one cost scalar per rank feeding the balancing plan).
+A step = one LoadBalancedChemistryModel::solve(deltaT): every cell integrated over deltaT = 1e-6 s from
+deltaTChem = 1e-7 s (reference tests/src/standardChemistryModel-Test.C:84).
+
+  value  device-resident: inputs already in HBM, CUDA events around K steps, max over ranks
+  e2e    through lbchem_solve_batch_host with pinned HOST buffers (H2D + integrate + D2H inside the timing)
+  --impl reference : the CPU oracle (restatement of the reference's solveCell path; the reference itself
+                     needs OpenFOAM and cannot be built here) on all host cores, bounded sample per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "cell-chemistry solves/s (GRI-3.0, 1 flow step)"
+UNIT = "cells/s"
+SOLVERS = {"seulex": ("seulex", 1e-12, 1e-1), "Rosenbrock34": ("Rosenbrock34", 1e-12, 1e-2)}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cells", type=int, default=1_000_000, help="cells per GPU")
+    ap.add_argument("--solver", default="seulex", choices=list(SOLVERS))
+    ap.add_argument("--workload", default="gri_uniform", choices=["gri_uniform", "gri_skewed"])
+    ap.add_argument("--cpu-sample", type=int, default=0, help="cells in the CPU baseline sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def make_workload(name, n, rank):
+    from loadbalancedchemistrymodel_b200 import workloads as W
+    if name == "gri_skewed":
+        return W.gri_skewed(n, rank=rank)
+    return W.gri_uniform(n, rank=rank)
+
+
+def config_dict(args, n_gpus, extra=None):
+    s, atol, rtol = SOLVERS[args.solver]
+    cfg = {
+        "workload": f"{args.workload}: GRI-Mech 3.0 (53 species, 325 reactions), {args.cells} synthetic cells per GPU "
+                    f"(BASELINE config 3; fixture cells T>1500 K resampled + noise, seed 1003)",
+        "mechanism": "GRI-3.0", "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
+        "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": f"cells sharded over {n_gpus} GPU(s), no data-path collective",
+        "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
+    }
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+def cpu_oracle_rate(args, n_sample, nthreads, steps=1, warmup=0):
+    """Oracle throughput on a bounded sample of the same workload, all host threads."""
+    from loadbalancedchemistrymodel_b200 import capi
+    from oracle import oracle as O
+    s, atol, rtol = SOLVERS[args.solver]
+    mech, Y, T, p, rho = make_workload(args.workload, n_sample, rank=0)
+    om = O.OracleModel(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol))
+    for _ in range(warmup):
+        om.solve_batch(Y, T, p, rho, 1e-6, 1e-7, nthreads=nthreads)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        r = om.solve_batch(Y, T, p, rho, 1e-6, 1e-7, nthreads=nthreads)
+    dt = (time.perf_counter() - t0) / steps
+    return n_sample / dt, dt, r["counters"]
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n_sample = args.cpu_sample or min(args.cells, 600 * cores)
+    rate, dt, _ = cpu_oracle_rate(args, n_sample, cores, steps=args.steps, warmup=args.warmup)
+    sample = f"{n_sample} cells of the workload per step, {cores} threads, static contiguous partition"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic", "config": config_dict(args, args.gpus),
+        "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "note": "CPU oracle = restatement of the reference's solveCell + OpenFOAM ODE stack (reference needs OpenFOAM; unbuildable here)",
+    }
+    print(json.dumps(line))
+
+
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                       "-lms", "200"], stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except Exception:
+            self.p.kill()
+        self.f.flush(); self.f.seek(0)
+        sm, mx, reasons = [], [], set()
+        for ln in self.f.read().splitlines():
+            c = [x.strip() for x in ln.split(",")]
+            if len(c) < 9:
+                continue
+            try:
+                sm.append(float(c[1])); mx.append(float(c[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), c[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if sm:
+            out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": float(max(mx)), "reasons": sorted(reasons), "samples": len(sm)}
+        try:
+            os.unlink(self.f.name)
+        except OSError:
+            pass
+        return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from loadbalancedchemistrymodel_b200 import capi
+    from loadbalancedchemistrymodel_b200 import workloads as W
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device (there is no CPU fallback)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    s, atol, rtol = SOLVERS[args.solver]
+    n = args.cells
+    mech, Y, T, p, rho = make_workload(args.workload, n, rank)
+    nSp = mech.n_species
+    chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol), device=local)
+
+    def pinned(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t
+
+    hY, hT, hp, hrho = pinned(Y), pinned(T), pinned(p), pinned(rho)
+    dY, dT_, dp, drho = (t.to(dev, non_blocking=True) for t in (hY, hT, hp, hrho))
+    dtc0 = torch.full((n,), W.DELTA_T_CHEM0, dtype=torch.float64, device=dev)
+    dtc = torch.empty_like(dtc0)
+    dRR = torch.empty((nSp, n), dtype=torch.float64, device=dev)
+    dTout = torch.empty(n, dtype=torch.float64, device=dev)
+    dcost = torch.empty(n, dtype=torch.float64, device=dev)
+    dstatus = torch.empty(n, dtype=torch.int32, device=dev)
+    gathered = torch.zeros(world, dtype=torch.float64, device=dev)
+    cells_per_rank = np.full(world, n, np.int32)
+    torch.cuda.synchronize()
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step_device():
+        # one LoadBalancedChemistryModel::solve(deltaT): integrate every local cell, sum the per-cell cost,
+        # all-gather it and derive the balancing plan for the next step (reference .C:512-519, :701)
+        dtc.copy_(dtc0)
+        chem.solve_device(n, n, dY, dT_, dp, drho, W.DELTA_T, dtc, dRR, dTout, dcost, dstatus, stream=stream)
+        if world > 1:
+            tot = dcost.sum().reshape(1)
+            dist.all_gather_into_tensor(gathered, tot)
+            capi.balance_plan(gathered.cpu().numpy(), cells_per_rank)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step_device()
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    kernel_ms = []
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step_device()
+    e1.record()
+    barrier()
+    ms = e0.elapsed_time(e1)
+    st = chem.stats()                      # counters + CUDA-event duration of the last integration kernel
+    kernel_ms.append(st["kernel_ms"])
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    ms_per_step = ms / args.steps
+    value = n * world / (ms_per_step * 1e-3)
+    n_failed = int(st["n_failed"])
+
+    # ---- end to end: pinned host buffers through the C ABI (H2D, integrate, D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        out = {"RR": pinned(np.empty((nSp, n))).numpy(), "T": pinned(np.empty(n)).numpy(), "cost": pinned(np.empty(n)).numpy(),
+               "status": pinned(np.empty(n, np.int32)).numpy(), "deltaTChem": pinned(np.empty(n)).numpy()}
+        args_h = (hY.numpy(), hT.numpy(), hp.numpy(), hrho.numpy(), W.DELTA_T, W.DELTA_T_CHEM0)
+        for _ in range(2):
+            chem.solve_host(*args_h, out=out)
+        barrier()
+        t0 = time.perf_counter()
+        ke = args.steps
+        for _ in range(ke):
+            r = chem.solve_host(*args_h, out=out)
+            _ = float(r["cost"].sum())            # the step's result read on the host
+        barrier()
+        el = (time.perf_counter() - t0) / ke
+        t = torch.tensor([el], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        el = float(t.item())
+        h2d = (nSp + 4) * n * 8
+        d2h = (nSp + 3) * n * 8 + n * 4
+        e2e = {"value": n * world / el, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": el * 1e3, "timing": "host wall clock around lbchem_solve_batch_host (blocking), max over ranks"}
+    clocks = sampler.stop() if sampler else None
+
+    if rank == 0:
+        # ---- roofline of the dominant (only) kernel: FP64 pipe; HBM figure beside it
+        model = W.flop_model(mech)
+        flops = W.algorithmic_flops(model, st)
+        k_ms = float(np.mean(kernel_ms))
+        peak = capi.fp64_peak(local, 300.0)
+        ach = flops / (k_ms * 1e-3) / 1e12
+        peaks = {}
+        try:
+            peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+        hbm_ach = 912.0 * n / (k_ms * 1e-3) / 1e9
+        roofline = {
+            "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
+            "kernel": "integrate_kernel<64>", "kernel_ms": k_ms,
+            "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
+            "flops_per_cell": flops / n, "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts",
+            "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
+                    "bytes_per_cell": 912, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+        }
+        cpu = None
+        if not args.no_cpu_baseline and world >= 1:
+            cores = os.cpu_count() or 1
+            n_sample = args.cpu_sample or min(n, 600 * cores)
+            rate, dtc_s, _ = cpu_oracle_rate(args, n_sample, cores)
+            cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
+                   "sample": f"{n_sample} cells of the same workload, one pass, {cores} threads ({dtc_s:.1f} s)"}
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+            "data": "synthetic", "config": config_dict(args, world), "clocks": clocks, "e2e": e2e,
+            "gpu_launches": args.steps * 1, "roofline": roofline, "cpu_baseline": cpu,
+            "stats_last_step": {k: int(v) for k, v in st.items() if k.startswith("n_")}, "failed_cells": n_failed,
+        }
+        print(json.dumps(line))
+    chem.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
