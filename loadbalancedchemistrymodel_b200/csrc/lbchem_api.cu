@@ -12,7 +12,14 @@
 
 #include "../../include/lbchem.h"
 #include "lbchem_device.cuh"
+#include "lbchem_v2.cuh"
 
+int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err);
+int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
+bool lb_v2_supported_size(int nEqn);
+cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
+cudaError_t lb_v2_launch(int nEqn, int solver, int grid, int groups, size_t smemBytes, const V2Mech& M, const DevOpts& O,
+                         const BatchArgs& B, cudaStream_t s);
 size_t lb_work_doubles(const DevMech& M, int solver);
 cudaError_t lb_configure(int tpc, int groups, size_t smemBytes, int* ctasPerSM);
 cudaError_t lb_launch_integrate(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const DevMech& M,
@@ -56,6 +63,10 @@ struct lbchem_handle_t {
     int tpc = 64, groups = 1, ctasPerSM = 1;
     size_t wsDoubles = 0, smemBytes = 0;
     int configuredSolver = -1, configuredTpc = -1;
+    V2Mech V2{};                     // packed mechanism of the fast path
+    bool v2Built = false, useV2 = false;
+    int v2Groups = 0; size_t v2Smem = 0;
+    double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
     void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
     unsigned long long* dQueue = nullptr;
     unsigned long long* dStats = nullptr;
@@ -240,7 +251,28 @@ int build_jacobian_lists(lbchem_handle h, int tpc) {
     return LBCHEM_OK;
 }
 
+int configure_v2(lbchem_handle h) {
+    h->useV2 = false;
+    const lbchem_options& o = h->opts;
+    if (!h->v2Built || o.threads_per_cell != 0 || getenv("LBCHEM_GENERAL_KERNEL")) return LBCHEM_OK;
+    if (o.solver != LBCHEM_SOLVER_SEULEX && o.solver != LBCHEM_SOLVER_ROSENBROCK34) return LBCHEM_OK;
+    if (!lb_v2_supported_size(h->V2.nEqn)) return LBCHEM_OK;
+    const size_t per = (size_t)lb_v2_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol) * sizeof(double);
+    if ((size_t)h->V2.blobBytes + per > h->smemMax) return LBCHEM_OK;
+    int groups = (int)std::min<size_t>(6, (h->smemMax - h->V2.blobBytes) / per);
+    if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
+    h->v2Groups = groups;
+    h->v2Smem = (size_t)h->V2.blobBytes + per * groups;
+    CK(lb_v2_configure(h->V2.nEqn, o.solver, h->v2Smem));
+    h->useV2 = true;
+    return LBCHEM_OK;
+}
+
 int configure(lbchem_handle h) {
+    {
+        int rc = configure_v2(h);
+        if (rc != LBCHEM_OK) return rc;
+    }
     int tpc = h->opts.threads_per_cell;
     if (tpc == 0) tpc = (h->M.nEqn <= 32) ? 32 : 64;
     if (tpc != 32 && tpc != 64) return fail(h, LBCHEM_E_INVALID, "threads_per_cell must be 0, 32 or 64");
@@ -318,6 +350,12 @@ int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) 
     lbchem_default_options(&h->opts);
     int rc = build_mechanism(h, mech);
     if (rc != LBCHEM_OK) return rc;
+    {
+        std::string e;
+        const int r2 = lb_v2_build(mech, &h->V2, h->allocs, e);
+        if (r2 < 0) return fail(h, r2, e);
+        h->v2Built = (r2 == 0);
+    }
     CK(cudaMalloc(&h->dQueue, sizeof(unsigned long long)));
     CK(cudaMalloc(&h->dStats, 8 * sizeof(unsigned long long)));
     CK(cudaMemset(h->dStats, 0, 8 * sizeof(unsigned long long)));
@@ -374,6 +412,15 @@ static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, 
     B.deltaTChem = deltaTChem; B.RR = RR; B.Tout = Tout; B.cost = cost; B.status = status; B.order = nullptr;
     B.queue = queue; B.stats = h->dStats;
     CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
+    if (h->useV2) {
+        long long grid2 = h->nSM;
+        const long long need2 = (n + h->v2Groups - 1) / h->v2Groups;
+        if (grid2 > need2) grid2 = need2;
+        if (grid2 < 1) grid2 = 1;
+        CK(lb_v2_launch(h->V2.nEqn, h->opts.solver, (int)grid2, h->v2Groups, h->v2Smem, h->V2, h->O, B, s));
+        h->launches++;
+        return LBCHEM_OK;
+    }
     long long grid = (long long)h->nSM * h->ctasPerSM;
     const long long need = (n + h->groups - 1) / h->groups;
     if (grid > need) grid = need;

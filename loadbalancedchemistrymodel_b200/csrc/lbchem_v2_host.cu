@@ -1,0 +1,279 @@
+// lbchem_v2_host.cu — packs a lbchem_mech_desc into the V2Mech blob + Jacobian gather program.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/lbchem.h"
+#include "lbchem_v2.cuh"
+
+namespace {
+
+struct Blob {
+    std::vector<unsigned char> b;
+    template <class T>
+    int add(const std::vector<T>& v) {
+        while (b.size() % 8) b.push_back(0);
+        const int off = (int)b.size();
+        const unsigned char* p = reinterpret_cast<const unsigned char*>(v.data());
+        b.insert(b.end(), p, p + v.size() * sizeof(T));
+        while (b.size() % 8) b.push_back(0);
+        return off;
+    }
+};
+
+std::vector<double> soa2(const double* a, int nSp, const int* idx, const double* div, int nq) {
+    std::vector<double> v((size_t)nq * nSp);
+    for (int i = 0; i < nSp; ++i)
+        for (int q = 0; q < nq; ++q) v[(size_t)q * nSp + i] = a[7 * i + idx[q]] / div[q];
+    return v;
+}
+
+bool small_int(double x, int lo, int hi) { return x == std::floor(x) && x >= lo && x <= hi; }
+
+}  // namespace
+
+// returns 0 = built, 1 = mechanism outside the fast path's class (caller keeps the general kernel), <0 = error
+int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err) {
+    const int nSp = m->n_species, nR = m->n_reactions, nEff = m->n_eff;
+    const int N = nSp + 2;
+    if (N > 64 || nSp > 254 || nR > 32000 || nEff > 31 || nR < 1) return 1;
+    V2Mech M{};
+    M.nSp = nSp; M.nR = nR; M.nEqn = N; M.nEff = nEff;
+
+    // ---- reaction order: homogeneous rounds of 64 (exp / no exp / irreversible / third body / fall-off)
+    std::vector<int> order(nR), posOf(nR);
+    auto cls = [&](int r) {
+        if (m->rtype[r] >= LBCHEM_R_FALLOFF_LINDEMANN) return 4;
+        if (m->rtype[r] == LBCHEM_R_THIRD_BODY) return 3;
+        if (!m->reversible[r]) return 2;
+        const bool hasExp = std::fabs(m->arr[3 * r + 1]) > 1e-300 || std::fabs(m->arr[3 * r + 2]) > 1e-300;
+        return hasExp ? 0 : 1;
+    };
+    for (int r = 0; r < nR; ++r) order[r] = r;
+    std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cls(a) < cls(b); });
+    for (int p = 0; p < nR; ++p) posOf[order[p]] = p;
+
+    std::vector<double> tcTab;
+    std::vector<double> A(nR), beta(nR), Ta(nR), fall;
+    std::vector<uint32_t> info(nR);
+    std::vector<unsigned long long> lpk(nR), rpk(nR);
+    int nFall = 0;
+    for (int p = 0; p < nR; ++p) {
+        const int r = order[p];
+        A[p] = m->arr[3 * r]; beta[p] = m->arr[3 * r + 1]; Ta[p] = m->arr[3 * r + 2];
+        const int nl = m->lhs_ptr[r + 1] - m->lhs_ptr[r], nr = m->rhs_ptr[r + 1] - m->rhs_ptr[r];
+        if (nl < 1 || nr < 1 || nl > 4 || nr > 4) return 1;
+        double dn = 0; int sumL = 0, sumR = 0;
+        unsigned long long lp = 0, rp = 0;
+        for (int s = 0; s < nl; ++s) {
+            const int k = m->lhs_ptr[r] + s;
+            if (!small_int(m->lhs_nu[k], 1, 7) || !small_int(m->lhs_exp[k], 1, 3)) return 1;
+            lp |= (unsigned long long)((unsigned)m->lhs_species[k] | ((unsigned)m->lhs_nu[k] << 10) | ((unsigned)m->lhs_exp[k] << 13)) << (16 * s);
+            dn -= m->lhs_nu[k]; sumL += (int)m->lhs_exp[k];
+        }
+        for (int s = 0; s < nr; ++s) {
+            const int k = m->rhs_ptr[r] + s;
+            if (!small_int(m->rhs_nu[k], 1, 7) || !small_int(m->rhs_exp[k], 1, 3)) return 1;
+            rp |= (unsigned long long)((unsigned)m->rhs_species[k] | ((unsigned)m->rhs_nu[k] << 10) | ((unsigned)m->rhs_exp[k] << 13)) << (16 * s);
+            dn += m->rhs_nu[k]; sumR += (int)m->rhs_exp[k];
+        }
+        if (sumL > 4 || sumR > 4 || !small_int(dn, -3, 3)) return 1;
+        lpk[p] = lp; rpk[p] = rp;
+        const double rtc = m->Tcommon[m->lhs_species[m->lhs_ptr[r]]];
+        int tci = (int)(std::find(tcTab.begin(), tcTab.end(), rtc) - tcTab.begin());
+        if (tci == (int)tcTab.size()) tcTab.push_back(rtc);
+        if (tci > 7) return 1;
+        const int rtype = m->rtype[r];
+        int fi = 0, eff = 0;
+        if (rtype != LBCHEM_R_ARRHENIUS) {
+            eff = m->eff_index[r];
+            if (eff < 0 || eff >= nEff) { err = "eff_index out of range"; return LBCHEM_E_INVALID; }
+        }
+        if (rtype >= LBCHEM_R_FALLOFF_LINDEMANN) {
+            if (nFall > 255) return 1;
+            fi = nFall++;
+            for (int q = 0; q < 3; ++q) fall.push_back(m->arr0[3 * r + q]);
+            for (int q = 0; q < 4; ++q) fall.push_back(m->troe[4 * r + q]);
+            fall.push_back(0.0);
+        }
+        const bool hasExp = std::fabs(beta[p]) > 1e-300 || std::fabs(Ta[p]) > 1e-300;
+        info[p] = (unsigned)rtype | ((unsigned)(m->reversible[r] ? 1 : 0) << 2) | ((unsigned)nl << 3) | ((unsigned)nr << 6) |
+                  ((unsigned)eff << 9) | ((unsigned)tci << 14) | ((unsigned)((int)dn + 3) << 17) | ((unsigned)fi << 20) |
+                  ((unsigned)(hasExp ? 1 : 0) << 28);
+    }
+    M.nFall = nFall; M.nTc = (int)tcTab.size();
+    while (tcTab.size() < 8) tcTab.push_back(0.0);
+
+    Blob B;
+    {
+        const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
+        const int haI[6] = {4, 3, 2, 1, 0, 5}; const double haD[6] = {5, 4, 3, 2, 1, 1};
+        const int sI[6] = {4, 3, 2, 1, 0, 6};  const double sD[6] = {4, 3, 2, 1, 1, 1};
+        M.oW = B.add(std::vector<double>(m->W, m->W + nSp));
+        M.oTc = B.add(std::vector<double>(m->Tcommon, m->Tcommon + nSp));
+        M.oCpLo = B.add(soa2(m->janaf_low, nSp, cpI, cpD, 5)); M.oCpHi = B.add(soa2(m->janaf_high, nSp, cpI, cpD, 5));
+        M.oHaLo = B.add(soa2(m->janaf_low, nSp, haI, haD, 6)); M.oHaHi = B.add(soa2(m->janaf_high, nSp, haI, haD, 6));
+        M.oSLo = B.add(soa2(m->janaf_low, nSp, sI, sD, 6));    M.oSHi = B.add(soa2(m->janaf_high, nSp, sI, sD, 6));
+    }
+    M.oA = B.add(A); M.oBeta = B.add(beta); M.oTa = B.add(Ta); M.oInfo = B.add(info);
+    M.oLpk = B.add(lpk); M.oRpk = B.add(rpk);
+    if (fall.empty()) fall.push_back(0.0);
+    M.oFall = B.add(fall); M.oTcTab = B.add(tcTab);
+
+    // sparse third-body efficiencies: M_e = sum_i c_i + sum_{eff != 1} (eff - 1) c_i
+    {
+        std::vector<int> effPtr(nEff + 1, 0), effSp; std::vector<double> effVal;
+        for (int e = 0; e < nEff; ++e) {
+            for (int i = 0; i < nSp; ++i) {
+                const double v = m->eff[(size_t)e * nSp + i];
+                if (v != 1.0) { effSp.push_back(i); effVal.push_back(v - 1.0); }
+            }
+            effPtr[e + 1] = (int)effSp.size();
+        }
+        if (effSp.empty()) { effSp.push_back(0); effVal.push_back(0.0); }
+        M.oEffPtr = B.add(effPtr); M.oEffSp = B.add(effSp); M.oEffVal = B.add(effVal);
+    }
+
+    // omega gather lists: species-major, ORIGINAL reaction order, lhs before rhs (the reference's accumulation order)
+    {
+        std::vector<int> spPtr(nSp + 1, 0); std::vector<uint32_t> spList;
+        std::vector<std::vector<uint32_t>> L(nSp);
+        for (int r = 0; r < nR; ++r) {
+            for (int k = m->lhs_ptr[r]; k < m->lhs_ptr[r + 1]; ++k)
+                L[m->lhs_species[k]].push_back((uint32_t)posOf[r] | ((uint32_t)(uint8_t)(int8_t)(-(int)m->lhs_nu[k]) << 16));
+            for (int k = m->rhs_ptr[r]; k < m->rhs_ptr[r + 1]; ++k)
+                L[m->rhs_species[k]].push_back((uint32_t)posOf[r] | ((uint32_t)(uint8_t)(int8_t)((int)m->rhs_nu[k]) << 16));
+        }
+        for (int i = 0; i < nSp; ++i) { spList.insert(spList.end(), L[i].begin(), L[i].end()); spPtr[i + 1] = (int)spList.size(); }
+        M.oSpPtr = B.add(spPtr); M.oSpList = B.add(spList);
+    }
+
+    // Jacobian entries (row, col) -> gather terms in the reference's accumulation order
+    struct Term { int kidx, s[3]; int coef; };
+    std::map<std::pair<int, int>, std::vector<Term>> E;
+    for (int r = 0; r < nR; ++r) {
+        for (int side = 0; side < 2; ++side) {
+            const int32_t* ptr = side ? m->rhs_ptr : m->lhs_ptr;
+            const int32_t* spc = side ? m->rhs_species : m->lhs_species;
+            const double* ex = side ? m->rhs_exp : m->lhs_exp;
+            if (side == 1 && !m->reversible[r]) continue;      // kr == 0: contributes exact zeros
+            const int b = ptr[r], e = ptr[r + 1];
+            for (int j = b; j < e; ++j) {
+                Term t; t.kidx = 2 * posOf[r] + side; int nf = 0;
+                for (int i = b; i < e; ++i) {
+                    const int reps = (int)ex[i] - (i == j ? 1 : 0);
+                    for (int q = 0; q < reps; ++q) { if (nf >= 3) return 1; t.s[nf++] = spc[i]; }
+                }
+                while (nf < 3) t.s[nf++] = nSp;                // CC[nSp] == 1.0
+                const int ej = (int)ex[j];
+                const int col = spc[j];
+                // d(omega)/dc_col = +kf-term for side 0, -kr-term for side 1; species on the lhs lose, rhs gain
+                for (int k = m->lhs_ptr[r]; k < m->lhs_ptr[r + 1]; ++k) {
+                    Term u = t; u.coef = (side == 0 ? -1 : 1) * (int)m->lhs_nu[k] * ej;
+                    E[{m->lhs_species[k], col}].push_back(u);
+                }
+                for (int k = m->rhs_ptr[r]; k < m->rhs_ptr[r + 1]; ++k) {
+                    Term u = t; u.coef = (side == 0 ? 1 : -1) * (int)m->rhs_nu[k] * ej;
+                    E[{m->rhs_species[k], col}].push_back(u);
+                }
+            }
+        }
+    }
+    // irreversible reactions still own the (row, col) entries of their rhs columns in the oracle (zeros); they
+    // only matter structurally, and a structural zero equals an absent entry for the LU build.
+    const int nEnt = (int)E.size();
+    M.nEnt = nEnt;
+    std::vector<int> rowPtr(N + 1, 0); std::vector<unsigned char> entCol;
+    std::vector<int> entTerms;
+    {
+        int row = 0;
+        for (auto& kv : E) {
+            while (row < kv.first.first) rowPtr[++row] = (int)entCol.size();
+            entCol.push_back((unsigned char)kv.first.second);
+            entTerms.push_back((int)kv.second.size());
+        }
+        while (row < N) rowPtr[++row] = (int)entCol.size();
+    }
+    M.oRowPtr = B.add(rowPtr);
+    if (entCol.empty()) entCol.push_back(0);
+    M.oEntCol = B.add(entCol);
+
+    // deal entries to the 64 threads in contiguous runs balanced by term count
+    std::vector<int> thrEnt(V2_TPC + 1, nEnt), thrN(V2_TPC, 0);
+    {
+        double total = 0; for (int c : entTerms) total += c + 1.0;
+        double acc = 0; int t = 0; thrEnt[0] = 0;
+        for (int e = 0; e < nEnt; ++e) {
+            while (t + 1 < V2_TPC && acc >= total * (t + 1) / V2_TPC) thrEnt[++t] = e;
+            acc += entTerms[e] + 1.0;
+        }
+        while (t + 1 <= V2_TPC) thrEnt[++t] = nEnt;
+    }
+    std::vector<std::vector<unsigned long long>> perThr(V2_TPC);
+    {
+        int e = 0;
+        for (auto& kv : E) {
+            int t = 0; while (!(e >= thrEnt[t] && e < thrEnt[t + 1])) ++t;
+            for (size_t q = 0; q < kv.second.size(); ++q) {
+                const Term& u = kv.second[q];
+                unsigned long long w = (unsigned long long)u.kidx | ((unsigned long long)u.s[0] << 16) | ((unsigned long long)u.s[1] << 24) |
+                                       ((unsigned long long)u.s[2] << 32) | ((unsigned long long)(uint8_t)(int8_t)u.coef << 40);
+                if (q + 1 == kv.second.size()) w |= 1ull << 48;
+                perThr[t].push_back(w);
+            }
+            ++e;
+        }
+    }
+    int maxT = 1;
+    for (int t = 0; t < V2_TPC; ++t) { thrN[t] = (int)perThr[t].size(); maxT = std::max(maxT, thrN[t]); }
+    std::vector<unsigned long long> jterm((size_t)maxT * V2_TPC, 0ull);
+    for (int t = 0; t < V2_TPC; ++t)
+        for (int k = 0; k < thrN[t]; ++k) jterm[(size_t)k * V2_TPC + t] = perThr[t][k];
+    M.jMaxTerms = maxT;
+    M.blobBytes = (int)B.b.size();
+
+    auto up = [&](const void* src, size_t bytes, const void** dst) -> bool {
+        void* d = nullptr;
+        if (cudaMalloc(&d, bytes ? bytes : 8) != cudaSuccess) return false;
+        allocs.push_back(d);
+        if (bytes && cudaMemcpy(d, src, bytes, cudaMemcpyHostToDevice) != cudaSuccess) return false;
+        *dst = d;
+        return true;
+    };
+    const void *dBlob, *dTerm, *dEnt, *dN;
+    if (!up(B.b.data(), B.b.size(), &dBlob) || !up(jterm.data(), jterm.size() * 8, &dTerm) ||
+        !up(thrEnt.data(), thrEnt.size() * 4, &dEnt) || !up(thrN.data(), thrN.size() * 4, &dN)) {
+        err = "cudaMalloc/cudaMemcpy failed while uploading the packed mechanism";
+        return LBCHEM_E_CUDA;
+    }
+    M.blob = static_cast<const unsigned char*>(dBlob);
+    M.jterm = static_cast<const unsigned long long*>(dTerm);
+    M.jthrEnt = static_cast<const int*>(dEnt);
+    M.jthrN = static_cast<const int*>(dN);
+    *out = M;
+    return 0;
+}
+
+// per-cell workspace (doubles) of the fast path; must match carve_v2 in lbchem_kernels_v2.cu
+int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol) {
+    const int N = M.nEqn, nSp = M.nSp;
+    int tb = 0;
+    if (solver == LBCHEM_SOLVER_SEULEX) {
+        int kt = (int)(-std::log10(relTol + absTol) * 0.6 + 0.5);
+        kt = std::max(1, std::min(10, kt));
+        tb = std::min(11, kt + 4);
+    }
+    M.tbRows = tb;
+    const int nBlk = (N + V2_BLK - 1) / V2_BLK;
+    int luAux = nBlk * (V2_LSTRIDE + V2_USTRIDE) + 4 * (N + 2);      // LB, UB, pivot-row buffers [2 warps][2 parities]
+    if (luAux < 2 * M.nR) luAux = 2 * M.nR;                            // aliased by KF/KR during the Jacobian
+    int d = 10 * N + tb * N + (nSp + 1) + 2 * nSp + M.nEff + M.nR + M.nEnt + nSp   // vectors, TB, CC, GL, GH, ME, OM, JS, JT
+            + 2 * N + 16 + luAux + 16 + 16;                                         // RD, BSH, XS, luAux, exchange slots, reduction scratch
+    d = (d + 1) & ~1;
+    M.wsDoubles = d;
+    return d;
+}

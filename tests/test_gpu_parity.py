@@ -85,12 +85,14 @@ def test_probes_match_oracle(gri, flame):
     chem.close()
 
 
+@pytest.mark.parametrize("tpc", [0, 64], ids=["fast", "general"])
 @pytest.mark.parametrize("solver,rel_tol", [("Rosenbrock34", 1e-2), ("seulex", 1e-1)])
-def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol):
-    """All 4000 cells of the reference's flame fixture, both tolerance sets of BASELINE config 3."""
+def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol, tpc):
+    """All 4000 cells of the reference's flame fixture, both tolerance sets of BASELINE config 3, through the
+    fast kernel (register LU, threads_per_cell = 0) and the general kernel (threads_per_cell = 64)."""
     sel = np.arange(flame["T"].shape[0])
     Y, T, p, rho = _state(gri, flame, sel)
-    opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol)
+    opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, threads_per_cell=tpc)
     chem = capi.Chemistry(gri, opts)
     got = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
     st = chem.stats()
