@@ -18,6 +18,12 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
 int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
 bool lb_v2_supported_size(int nEqn);
 cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
+int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
+bool lb_v3_supported(const V2Mech& M);
+int lb_v3_ctx_bytes();
+cudaError_t lb_v3_configure(int solver, size_t smemBytes);
+cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
+                         const BatchArgs& B, cudaStream_t s);
 cudaError_t lb_v2_launch(int nEqn, int solver, int grid, int groups, size_t smemBytes, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s);
 size_t lb_work_doubles(const DevMech& M, int solver);
@@ -64,7 +70,8 @@ struct lbchem_handle_t {
     size_t wsDoubles = 0, smemBytes = 0;
     int configuredSolver = -1, configuredTpc = -1;
     V2Mech V2{};                     // packed mechanism of the fast path
-    bool v2Built = false, useV2 = false;
+    bool v2Built = false, useV2 = false, useV3 = false;
+    int v3Groups = 0, v3Ws = 0; size_t v3Smem = 0;
     int v2Groups = 0; size_t v2Smem = 0;
     double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
     void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
@@ -252,10 +259,26 @@ int build_jacobian_lists(lbchem_handle h, int tpc) {
 }
 
 int configure_v2(lbchem_handle h) {
-    h->useV2 = false;
+    h->useV2 = false; h->useV3 = false;
     const lbchem_options& o = h->opts;
     if (!h->v2Built || o.threads_per_cell != 0 || getenv("LBCHEM_GENERAL_KERNEL")) return LBCHEM_OK;
     if (o.solver != LBCHEM_SOLVER_SEULEX && o.solver != LBCHEM_SOLVER_ROSENBROCK34) return LBCHEM_OK;
+    // kernel generation: v3 (compact code, shared-memory LU) unless LBCHEM_KERNEL=v2 asks for the register-LU kernel
+    const char* gen = getenv("LBCHEM_KERNEL");
+    if (!(gen && !strcmp(gen, "v2")) && lb_v3_supported(h->V2)) {
+        const int ws = lb_v3_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol);
+        const size_t per3 = (size_t)ws * sizeof(double);
+        const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.blobBytes;
+        if (fixed + per3 <= h->smemMax) {
+            int groups = (int)std::min<size_t>(4, (h->smemMax - fixed) / per3);
+            if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
+            h->v3Groups = groups; h->v3Ws = ws;
+            h->v3Smem = fixed + per3 * groups;
+            CK(lb_v3_configure(o.solver, h->v3Smem));
+            h->useV3 = true;
+            return LBCHEM_OK;
+        }
+    }
     if (!lb_v2_supported_size(h->V2.nEqn)) return LBCHEM_OK;
     const size_t per = (size_t)lb_v2_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol) * sizeof(double);
     if ((size_t)h->V2.blobBytes + per > h->smemMax) return LBCHEM_OK;
@@ -412,6 +435,15 @@ static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, 
     B.deltaTChem = deltaTChem; B.RR = RR; B.Tout = Tout; B.cost = cost; B.status = status; B.order = nullptr;
     B.queue = queue; B.stats = h->dStats;
     CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
+    if (h->useV3) {
+        long long grid3 = h->nSM;
+        const long long need3 = (n + h->v3Groups - 1) / h->v3Groups;
+        if (grid3 > need3) grid3 = need3;
+        if (grid3 < 1) grid3 = 1;
+        CK(lb_v3_launch(h->opts.solver, (int)grid3, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, s));
+        h->launches++;
+        return LBCHEM_OK;
+    }
     if (h->useV2) {
         long long grid2 = h->nSM;
         const long long need2 = (n + h->v2Groups - 1) / h->v2Groups;

@@ -1,0 +1,902 @@
+// lbchem_kernels_v3.cu — compact-code generation of the per-cell chemistry integration for sm_100a.
+//
+// Why: the v2 kernel (register-resident, fully unrolled LU) is 29 k SASS instructions; ncu shows 71 % of its
+// warp samples stalled on instruction fetch (profiles/r01_ncu_v2_seulex.txt). This kernel keeps every hot
+// phase a SHORT LOOP that stays resident in the 32 KB instruction cache:
+//   * the (I/(g dx) - J) matrix lives in shared memory (species block + temperature column, 53 x 54 for GRI;
+//     the T and p rows of OpenFOAM's Jacobian are zero, so those two equations decouple exactly),
+//     LU with implicit row pivoting: rows never move, one named barrier per column;
+//   * triangular solves are column loops over the same storage;
+//   * rate evaluation is split into passes with ONE exp() call site: (1) arguments of every Arrhenius and
+//     equilibrium exponential, (2) a flat loop exponentiating 2*nR values, (3) assembly of kf, kr and omega,
+//     fall-off reactions in their own loop.
+// Arithmetic (operation order inside each formula, elimination order, pivot tie rule) is that of v2, which
+// is parity-green against the oracle; see DESIGN.md.
+// 64 threads integrate one cell; a persistent CTA stages the packed mechanism (lbchem_v2.cuh) once.
+#include <cuda_runtime.h>
+#include <math.h>
+#include "lbchem_device.cuh"
+#include "lbchem_v2.cuh"
+#include "../../include/lbchem.h"
+
+namespace v3 {
+
+constexpr int TPC = 64;
+
+struct SMech {            // typed views into the staged blob
+    int nSp, nR, nEff;
+    const double *W, *Tc, *cpLo, *cpHi, *haLo, *haHi, *sLo, *sHi;
+    const double *A, *beta, *Ta, *fall, *tcTab, *effVal;
+    const unsigned* info; const unsigned long long *lpk, *rpk;
+    const int *effPtr, *effSp, *spPtr, *rowPtr;
+    const unsigned* spList; const unsigned char* entCol;
+};
+
+__device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned char* b) {
+    S.nSp = M.nSp; S.nR = M.nR; S.nEff = M.nEff;
+#define P(T, off) reinterpret_cast<const T*>(b + M.off)
+    S.W = P(double, oW); S.Tc = P(double, oTc); S.cpLo = P(double, oCpLo); S.cpHi = P(double, oCpHi);
+    S.haLo = P(double, oHaLo); S.haHi = P(double, oHaHi); S.sLo = P(double, oSLo); S.sHi = P(double, oSHi);
+    S.A = P(double, oA); S.beta = P(double, oBeta); S.Ta = P(double, oTa); S.fall = P(double, oFall);
+    S.tcTab = P(double, oTcTab); S.effVal = P(double, oEffVal);
+    S.info = P(unsigned, oInfo); S.lpk = P(unsigned long long, oLpk); S.rpk = P(unsigned long long, oRpk);
+    S.effPtr = P(int, oEffPtr); S.effSp = P(int, oEffSp); S.spPtr = P(int, oSpPtr); S.rowPtr = P(int, oRowPtr);
+    S.spList = P(unsigned, oSpList); S.entCol = P(unsigned char, oEntCol);
+#undef P
+}
+
+// Group-level helpers. Threads derive their coordinates from threadIdx; nothing lives in local memory, so the
+// heavy routines below can be real (non-inlined) functions with exactly one copy in the instruction stream.
+struct Grp {
+    int tid, gid, lane, warp;
+    double* red;      // 32 doubles of exchange scratch at the start of the group's workspace: 4 slots of 8
+    __device__ __forceinline__ Grp(double* base) {
+        tid = threadIdx.x % TPC; gid = threadIdx.x / TPC; lane = threadIdx.x & 31; warp = tid >> 5; red = base;
+    }
+    __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory"); }
+    // Reductions write slot `s` (0..3). Two reductions with no barrier in between must use different slots.
+    __device__ __forceinline__ void sum3(double& a, double& b, double& c, int s) const {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); c += __shfl_xor_sync(0xffffffffu, c, o);
+        }
+        double* r = red + 8 * s;
+        if (lane == 0) { r[warp * 3] = a; r[warp * 3 + 1] = b; r[warp * 3 + 2] = c; }
+        sync();
+        a = r[0] + r[3]; b = r[1] + r[4]; c = r[2] + r[5];
+    }
+    __device__ __forceinline__ double sum(double a, int s) const {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a;
+        sync();
+        return r[0] + r[1];
+    }
+    __device__ __forceinline__ double maxnan(double v, int s) const {   // max with NaN propagation
+        double bad = (v != v) ? 1.0 : 0.0;
+        v = (v != v) ? 0.0 : v;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o)); bad = fmax(bad, __shfl_xor_sync(0xffffffffu, bad, o));
+        }
+        double* r = red + 8 * s;
+        if (lane == 0) { r[warp * 2] = v; r[warp * 2 + 1] = bad; }
+        sync();
+        v = fmax(r[0], r[2]); bad = fmax(r[1], r[3]);
+        return bad > 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : v;
+    }
+    __device__ __forceinline__ int any(int p, int s) const {
+        const int a = __any_sync(0xffffffffu, p);
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a ? 1.0 : 0.0;
+        sync();
+        return (r[0] + r[1]) > 0.0;
+    }
+};
+
+// Per-CTA context in shared memory: mechanism views, options and the layout of a group's workspace
+// (offsets in doubles from the group's base). Every routine takes (cx, base).
+struct Ctx {
+    SMech S;
+    DevOpts O;
+    int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
+    int oV, oTB, oCC, oGL, oGH, oME, oOM, oE2, oJS, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA;
+    const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
+};
+enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N };
+
+__host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
+    const int N = M.nEqn;
+    int p = 32;                               // reduction scratch
+    c.oXCH = p; p += 16; c.oXS = p; p += 16; c.oCNT = p; p += 4;
+    c.oV = p; p += 10 * N;
+    c.oTB = p; p += M.tbRows * N;
+    c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
+    c.oOM = p; p += M.nR; c.oE2 = p; p += M.nR; c.oJS = p; p += M.nEnt; c.oJT = p; p += M.nSp;
+    c.oRD = p; p += N; c.oBS = p; p += N; c.oSTEP = p; p += (N + 1) / 2;
+    c.lda = (M.nSp + 1) | 1;                  // odd leading dimension: conflict-free column access across rows
+    c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
+    return (p + 1) & ~1;
+}
+#define WS(name) (base + cx->o##name)
+#define VEC(i) (base + cx->oV + (i) * cx->nEqn)
+
+// ---- janaf polynomials (Horner forms identical to the oracle) -----------------------------------
+__device__ __forceinline__ double jcp(const double* a, int st, double T) {
+    return (((a[4 * st] * T + a[3 * st]) * T + a[2 * st]) * T + a[1 * st]) * T + a[0];
+}
+__device__ __forceinline__ double jha(const double* q, int st, double T) {
+    return ((((q[0] * T + q[1 * st]) * T + q[2 * st]) * T + q[3 * st]) * T + q[4 * st]) * T + q[5 * st];
+}
+__device__ __forceinline__ double js(const double* q, int st, double T, double lnT) {
+    return (((q[0] * T + q[1 * st]) * T + q[2 * st]) * T + q[3 * st]) * T + q[4 * st] * lnT + q[5 * st];
+}
+
+__device__ __forceinline__ double cpow(double c, unsigned e) {   // e in 1..3
+    return e == 1 ? c : (e == 2 ? c * c : c * c * c);
+}
+
+__device__ __forceinline__ double side_product(const double* c, unsigned long long pk, unsigned n) {
+    double f = 1.0;
+#pragma unroll 1
+    for (unsigned s = 0; s < n; ++s) { const unsigned sl = V2_SLOT(pk, s); f *= cpow(c[V2_SP(sl)], V2_EX(sl)); }
+    return f;
+}
+
+// clamp c, refresh Gibbs functions and third-body sums for temperature T; ends with a group sync.
+// y: state vector (c, T, p). If `clamp` is false CC is taken as current (finite-difference passes).
+__device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* base, const double* y, double T, double lnT, bool clamp) {
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid;
+    double* CC = WS(CC);
+    double cs = 0.0;
+    if (t < nSp) {
+        if (clamp) { const double c = fmax(y[t], 0.0); CC[t] = c; cs = c; }
+        WS(GL)[t] = jha(S.haLo + t, nSp, T) - T * js(S.sLo + t, nSp, T, lnT);
+        WS(GH)[t] = jha(S.haHi + t, nSp, T) - T * js(S.sHi + t, nSp, T, lnT);
+    }
+    if (clamp) {
+        if (t == nSp) CC[nSp] = 1.0;
+        const double cTot = g.sum(cs, 0);           // barrier inside: CC, GL, GH visible afterwards
+        if (t < S.nEff) {
+            double m = cTot;
+#pragma unroll 1
+            for (int k = S.effPtr[t]; k < S.effPtr[t + 1]; ++k) m = fma(S.effVal[k], CC[S.effSp[k]], m);
+            WS(ME)[t] = m;
+        }
+    }
+    g.sync();
+}
+
+// omega of every reaction at (CC, T) into OM[pos]; keep != 0 also stores kf, kr (Jacobian assembly).
+// Pass structure (one exp call site): exponentials -> fall-off blending -> kf, kr, mass action.
+__device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int keep, double T, double lnT, double invT) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nR = S.nR, nFall = cx->nFall;
+    double *OM = WS(OM), *E2 = WS(E2);
+    const double *GL = WS(GL), *GH = WS(GH), *ME = WS(ME), *CC = WS(CC);
+    // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor), E2[p] = exp(-dG/RT) if reversible
+#pragma unroll 1
+    for (int i = g.tid; i < 2 * nR; i += TPC) {
+        const bool second = i >= nR;
+        const int p = second ? i - nR : i;
+        const unsigned iw = S.info[p];
+        double arg = 0.0, val = 1.0;
+        bool need;
+        if (!second) {
+            need = V2_HASEXP(iw);
+            if (need) arg = fma(S.beta[p], lnT, -S.Ta[p] * invT);
+        } else {
+            need = false;
+            if (V2_REV(iw)) {
+                const double* G = (T < S.tcTab[V2_TCI(iw)]) ? GL : GH;
+                const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
+                double gs = 0.0;
+#pragma unroll 1
+                for (unsigned s = 0; s < V2_NR(iw); ++s) { const unsigned sl = V2_SLOT(rp, s); gs = fma((double)V2_NU(sl), G[V2_SP(sl)], gs); }
+#pragma unroll 1
+                for (unsigned s = 0; s < V2_NL(iw); ++s) { const unsigned sl = V2_SLOT(lp, s); gs = fma(-(double)V2_NU(sl), G[V2_SP(sl)], gs); }
+                arg = -gs * invT;
+                need = arg < 600.0;
+                val = LB_VGREAT;
+            }
+        }
+        if (need) val = exp(arg);
+        (second ? E2 : OM)[p] = val;
+    }
+    g.sync();
+    // (2) fall-off reactions (sorted last): OM[p] <- blended rate constant
+    if (nFall > 0) {
+#pragma unroll 1
+        for (int q = g.tid; q < nFall; q += TPC) {
+            const int p = nR - nFall + q;
+            const unsigned iw = S.info[p];
+            const double* f = S.fall + 8 * V2_FALL(iw);
+            double k0 = f[0];
+            if (fabs(f[1]) > LB_VSMALL || fabs(f[2]) > LB_VSMALL) k0 *= exp(fma(f[1], lnT, -f[2] * invT));
+            const double kInf = S.A[p] * OM[p];
+            const double Pr = k0 * ME[V2_EFF(iw)] / kInf;
+            double F = 1.0;
+            if (V2_RTYPE(iw) == LBCHEM_R_FALLOFF_TROE) {
+                const double al = f[3], Tsss = f[4], Ts = f[5], Tss = f[6];
+                const double logFcent = log10(fmax((1 - al) * exp(-T / Tsss) + al * exp(-T / Ts) + exp(-Tss / T), LB_SMALL));
+                const double cc = -0.4 - 0.67 * logFcent;
+                const double nn = 0.75 - 1.27 * logFcent;
+                const double logPr = log10(fmax(Pr, LB_SMALL));
+                const double q2 = (logPr + cc) / (nn - 0.14 * (logPr + cc));
+                F = pow(10.0, logFcent / (1.0 + q2 * q2));
+            }
+            OM[p] = kInf * (Pr / (1 + Pr)) * F;
+        }
+        g.sync();
+    }
+    // (3) kf, kr, omega
+    const double x = LB_PSTD / (cx->O.RR * T);
+    const double kcFloor = cx->O.kcFloor;
+    double* KF = WS(A); double* KR = KF + nR;
+#pragma unroll 1
+    for (int p = g.tid; p < nR; p += TPC) {
+        const unsigned iw = S.info[p];
+        const unsigned ty = V2_RTYPE(iw);
+        double k = OM[p];
+        if (ty < LBCHEM_R_FALLOFF_LINDEMANN) {
+            k = S.A[p] * k;
+            if (ty == LBCHEM_R_THIRD_BODY) k = ME[V2_EFF(iw)] * k;
+        }
+        double kr = 0.0;
+        if (V2_REV(iw)) {
+            double Kc = E2[p];
+            const int dn = (int)V2_DNC(iw) - 3;
+            if (dn != 0) {
+                if (dn == 1) Kc *= x;
+                else if (dn == -1) Kc *= 1.0 / x;
+                else Kc *= pow(x, (double)dn);
+            }
+            kr = k / fmax(Kc, kcFloor);
+        }
+        const double f = k * side_product(CC, S.lpk[p], V2_NL(iw));
+        const double b = kr * side_product(CC, S.rpk[p], V2_NR(iw));
+        OM[p] = f - b;
+        if (keep) { KF[p] = k; KR[p] = kr; }
+    }
+    g.sync();
+}
+
+__device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
+    double acc = 0.0;
+    const int e = S.spPtr[i + 1];
+#pragma unroll 1
+    for (int k = S.spPtr[i]; k < e; ++k) {
+        const unsigned u = S.spList[k];
+        acc = fma((double)(int)(signed char)(u >> 16), om[u & 0xffffu], acc);
+    }
+    return acc;
+}
+
+// StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
+__device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid;
+    g.sync();
+    const double T = y[nSp];
+    const double lnT = log(T), invT = 1.0 / T;
+    prepare(g, cx, base, y, T, lnT, true);
+    reaction_sweep(cx, base, 0, T, lnT, invT);
+    const double RR = cx->O.RR;
+    double rho = 0.0, cp = 0.0, dT = 0.0;
+    if (t < nSp) {
+        const double d = gather_species(S, WS(OM), t);
+        dydt[t] = d;
+        const double ci = WS(CC)[t];
+        const bool lo = T < S.Tc[t];
+        rho = S.W[t] * ci;
+        cp = ci * (RR * jcp((lo ? S.cpLo : S.cpHi) + t, nSp, T));
+        dT = (RR * jha((lo ? S.haLo : S.haHi) + t, nSp, T)) * d;
+    }
+    g.sum3(rho, cp, dT, 1);
+    cp /= rho;
+    dT /= rho * cp;
+    if (t == 0) { dydt[nSp] = -dT; dydt[nSp + 1] = 0.0; reinterpret_cast<int*>(WS(CNT))[CNT_RHS]++; }
+    g.sync();
+}
+
+// StandardChemistryModel::jacobian (A.9) into the sparse store: JS[entry] (species block, structural
+// non-zeros in (row, col) order), JT[i] = d(dc_i/dt)/dT by central difference; dfdx = species rates (A.4 quirk)
+__device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid, N = cx->nEqn;
+    g.sync();
+    const double T = y[nSp];
+    const double delta = 1.0e-3;
+    double dp = 0.0;
+#pragma unroll 1
+    for (int pass = 0; pass < 3; ++pass) {
+        const double Tp = pass == 0 ? T : (pass == 1 ? T + delta : T - delta);
+        const double lnT = log(Tp), invT = 1.0 / Tp;
+        prepare(g, cx, base, y, Tp, lnT, pass == 0);
+        reaction_sweep(cx, base, pass == 0, Tp, lnT, invT);
+        if (pass == 0) {
+            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? gather_species(S, WS(OM), t) : 0.0;
+            // gather program: acc += coef * k * c1 * c2 * c3, entry closed by the `last` flag
+            const double* KFR = WS(A); const double* CC = WS(CC); double* JS = WS(JS);
+            const int nR = S.nR;
+            const int nT = cx->jthrN[t];
+            int e = cx->jthrEnt[t];
+            double acc = 0.0;
+            const unsigned long long* prog = cx->jterm + t;
+            unsigned long long wd = nT > 0 ? prog[0] : 0ull;
+#pragma unroll 1
+            for (int k = 0; k < nT; ++k) {
+                const unsigned long long nx = (k + 1 < nT) ? prog[(size_t)(k + 1) * V2_TPC] : 0ull;   // prefetch
+                const unsigned kid = V2_T_K(wd);
+                const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
+                const double d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
+                acc = fma((double)V2_T_COEF(wd), d, acc);
+                if (V2_T_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
+                wd = nx;
+            }
+        } else if (t < nSp) {
+            const double d = gather_species(S, WS(OM), t);
+            if (pass == 1) dp = d; else WS(JT)[t] = 0.5 * (dp - d) / delta;
+        }
+        g.sync();
+    }
+    if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_JAC]++;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dense linear algebra on the shared-memory matrix: thread t owns species row t of  dg*I - J
+// (columns 0..nSp: species block + temperature column). The T and p rows are (0 .. dg .. 0): handled in closed form.
+// ------------------------------------------------------------------------------------------------
+// Build the matrix from the sparse Jacobian and factorise it: LUDecompose (A.10) with implicit row scaling and
+// partial pivoting. Rows never move: `pos` is the index the row would have in the reference's physically swapped
+// matrix (drives its tie rule: the LAST maximal row wins), STEP[t] the column at which row t became the pivot row.
+__device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
+    double* A = WS(A);
+    double* RD = WS(RD);
+    int* STEP = reinterpret_cast<int*>(WS(STEP));
+    double* XCH = WS(XCH);
+    double* row = A + t * lda;
+    g.sync();
+    double big = fabs(dg);
+    if (t < nSp) {
+#pragma unroll 1
+        for (int k = 0; k <= nSp; ++k) row[k] = 0.0;
+        const double* JS = WS(JS);
+        const int e1 = S.rowPtr[t + 1];
+#pragma unroll 1
+        for (int e = S.rowPtr[t]; e < e1; ++e) row[S.entCol[e]] = -JS[e];
+        row[nSp] = -WS(JT)[t];
+        row[t] += dg;
+        big = 0.0;
+#pragma unroll 1
+        for (int k = 0; k <= nSp; ++k) big = fmax(big, fabs(row[k]));
+    }
+    if (g.any(t < N && big == 0.0, 2)) return LBCHEM_CELL_SINGULAR;
+    const double vv = 1.0 / big;
+    bool done = (t >= nSp);
+    int pos = t;
+    if (t >= nSp && t < N) { STEP[t] = t; RD[t] = 1.0 / dg; }
+#pragma unroll 1
+    for (int j = 0; j < nSp; ++j) {
+        const double piv = done ? 0.0 : row[j];
+        const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+        const bool c1 = hi == mh;
+        const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
+        const bool c2 = c1 && lo == ml;
+        const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
+        const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
+        const bool win = c2 && pp == mp;
+        const int par = j & 1;
+        if (win) {
+            double* slot = XCH + (g.warp * 2 + par) * 4;
+            slot[0] = __longlong_as_double((long long)key);
+            reinterpret_cast<int*>(slot + 1)[0] = pos;
+            reinterpret_cast<int*>(slot + 1)[1] = t;
+            slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
+        }
+        g.sync();
+        const double* s0 = XCH + (0 * 2 + par) * 4;
+        const double* s1 = XCH + (1 * 2 + par) * 4;
+        const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
+        const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
+        const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
+        const double* sw = (k1 > k0 || (k1 == k0 && p1 > p0)) ? s1 : s0;
+        const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
+        const int ptid = reinterpret_cast<const int*>(sw + 1)[1];
+        const double rd = sw[2];
+        if (t == ptid) {
+            done = true; STEP[t] = j; RD[j] = rd;
+            if (piv == 0.0) row[j] = LB_SMALL;
+        } else if (!done) {
+            if (pos == j) pos = ppos;
+            const double l = piv * rd;
+            row[j] = l;
+            const double* prow = A + ptid * lda;
+#pragma unroll 2
+            for (int k = j + 1; k <= nSp; ++k) row[k] = fma(-l, prow[k], row[k]);
+        }
+    }
+    if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
+    g.sync();
+    return 0;
+}
+
+// x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out)
+__device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
+    const Grp g(base);
+    const int nSp = cx->S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
+    const double* row = WS(A) + t * lda;
+    const double* RD = WS(RD);
+    double* BS = WS(BS);
+    g.sync();
+    const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
+    double bt = t < N ? x[t] : 0.0;
+    const bool sp = t < nSp;
+    // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
+#pragma unroll 1
+    for (int j = 0; j < nSp; ++j) {
+        if (step == j) BS[j] = bt;
+        g.sync();
+        if (sp && step > j) bt = fma(-row[j], BS[j], bt);
+    }
+    // backward substitution: p and T first (diagonal rows), then the species columns in descending order
+    if (t == nSp + 1) x[t] = bt * RD[t];
+    if (t == nSp) { const double v = bt * RD[t]; BS[t] = v; x[t] = v; }
+    g.sync();
+    if (sp) bt = fma(-row[nSp], BS[nSp], bt);
+#pragma unroll 1
+    for (int j = nSp - 1; j >= 0; --j) {
+        if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
+        g.sync();
+        if (sp && step < j) bt = fma(-row[j], BS[j], bt);
+    }
+    if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_SOLVE]++;
+    g.sync();
+}
+
+// ------------------------------------------------------------------------------------------------
+// integrators (control flow identical to lbchem_kernels_v2.cu; only the heavy routines are calls)
+// ------------------------------------------------------------------------------------------------
+struct Cell { int fail; double theta; int kTarg; };
+struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
+
+__constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
+__constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434, 625};
+
+#define CNT(i) (reinterpret_cast<int*>(WS(CNT))[i])
+
+// one Rosenbrock34 attempt (A.4) from Y0=V0 with step dx; result in V1. The sparse Jacobian (and dfdx in V3)
+// of the step start are re-used after a rejected attempt: the reference recomputes identical values.
+__device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dx) {
+    const double a21 = 2, a31 = 48.0 / 25.0, a32 = 6.0 / 25.0, c21 = -8, c31 = 372.0 / 25.0, c32 = 12.0 / 5.0,
+                 c41 = -112.0 / 125.0, c42 = -54.0 / 125.0, c43 = -2.0 / 5.0, b1 = 19.0 / 9.0, b2 = 1.0 / 2.0,
+                 b3 = 25.0 / 108.0, b4 = 125.0 / 108.0, e1 = 34.0 / 108.0, e2 = 7.0 / 36.0, e3 = 0, e4 = 125.0 / 108.0,
+                 gamma = 1.0 / 2.0, c1X = 1.0 / 2.0, c2X = -3.0 / 2.0, c3X = 121.0 / 50.0, c4X = 29.0 / 250.0;
+    const int t = g.tid, N = cx->nEqn;
+    double *Y0 = VEC(0), *Y = VEC(1), *D0 = VEC(2), *DX = VEC(3), *K1 = VEC(4), *K2 = VEC(5), *K3 = VEC(6), *K4 = VEC(7), *DY = VEC(8);
+    const int st = lu_factor(cx, base, 1.0 / (gamma * dx));
+    if (st) { cs.fail = st; return 0.0; }
+    if (t == 0) CNT(CNT_JAC)++;    // algorithmic count: the reference evaluates the Jacobian in every attempt
+#pragma unroll 1
+    for (int s = 0; s < 4; ++s) {
+        if (s == 1 || s == 2) {
+            if (t < N) Y[t] = (s == 1) ? Y0[t] + a21 * K1[t] : Y0[t] + a31 * K1[t] + a32 * K2[t];
+            derivatives(cx, base, Y, DY);
+        }
+        double* K = VEC(4 + s);
+        if (t < N) {
+            double r;
+            if (s == 0) r = D0[t] + dx * c1X * DX[t];
+            else if (s == 1) r = DY[t] + dx * c2X * DX[t] + c21 * K1[t] / dx;
+            else if (s == 2) r = DY[t] + dx * c3X * DX[t] + (c31 * K1[t] + c32 * K2[t]) / dx;
+            else r = DY[t] + dx * c4X * DX[t] + (c41 * K1[t] + c42 * K2[t] + c43 * K3[t]) / dx;
+            K[t] = r;
+        }
+        lu_solve(cx, base, K);
+    }
+    double em = 0.0;
+    if (t < N) {
+        const double yi = Y0[t] + b1 * K1[t] + b2 * K2[t] + b3 * K3[t] + b4 * K4[t];
+        const double er = e1 * K1[t] + e2 * K2[t] + e3 * K3[t] + e4 * K4[t];
+        Y[t] = yi;
+        em = fabs(er) / (cx->O.absTol + cx->O.relTol * fmax(fabs(Y0[t]), fabs(yi)));
+    }
+    return g.maxnan(em, 0);
+}
+
+// adaptiveSolver::solve (A.3)
+__device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, double& dxTry) {
+    const double safeScale = 0.9, alphaInc = 0.2, alphaDec = 0.25, minScale = 0.2, maxScale = 10;
+    const int t = g.tid, N = cx->nEqn;
+    double dx = dxTry, err = 0.0;
+    // dydx0 and the Jacobian are both evaluated at (y0, T0)
+    jacobian(cx, base, VEC(0), VEC(3));
+    if (t == 0) CNT(CNT_JAC)--;                 // counted per attempt in rosenbrock34_step
+    derivatives(cx, base, VEC(0), VEC(2));
+    do {
+        if (t == 0) CNT(CNT_ATTEMPTS)++;
+        err = rosenbrock34_step(g, cx, base, cs, dx);
+        if (cs.fail) return;
+        if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
+        if (err > 1) {
+            const double scale = fmax(safeScale * pow(err, -alphaDec), minScale);
+            dx *= scale;
+            if (dx < LB_VSMALL) { cs.fail = LBCHEM_CELL_UNDERFLOW; return; }
+        }
+    } while (err > 1);
+    x += dx;
+    g.sync();
+    if (t < N) VEC(0)[t] = VEC(1)[t];
+    g.sync();
+    if (err > pow(maxScale / safeScale, -1.0 / alphaInc))
+        dxTry = fmin(fmax(safeScale * pow(err, -alphaInc), minScale), maxScale) * dx;
+    else
+        dxTry = safeScale * maxScale * dx;
+}
+
+// seulex::seul (A.5): one extrapolation column; y0 = V4, scale = V5, result in V6.
+// `phase` keeps derivatives() and lu_solve() at one call site each: phase 1 = the stability check of the
+// second sub-step (solves dyc), phase 0 = the regular Euler increment (solves dy).
+__device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k) {
+    const int t = g.tid, N = cx->nEqn;
+    const int nSteps = c_nSeq[k];
+    const double dx = dxTot / nSteps;
+    double *y0 = VEC(4), *scale = VEC(5), *yOut = VEC(6), *dy = VEC(7), *yT = VEC(1), *f = VEC(8), *dyc = VEC(9);
+    const int st = lu_factor(cx, base, 1 / dx);
+    if (st) { cs.fail = st; return false; }
+    bool ok = true;
+    int it = 0, phase = 0;
+    double dy1 = 0.0;
+#pragma unroll 1
+    while (it < nSteps) {
+        if (phase == 0) {
+            if (it == 1) { if (t < N) yT[t] = y0[t] + dy[t]; }
+            else if (it > 1) { if (t < N) yT[t] += dy[t]; }
+            derivatives(cx, base, it == 0 ? y0 : yT, f);
+            if (it == 1 && k <= 1) phase = 1;
+        }
+        double* rhs;
+        if (phase == 1) {
+            double s1 = 0.0;
+            if (t < N) { const double q = dy[t] / scale[t]; s1 = q * q; dyc[t] = f[t] - dy[t] / dx; }
+            dy1 = sqrt(g.sum(s1, 2));
+            rhs = dyc;
+        } else {
+            if (t < N) dy[t] = f[t];
+            rhs = dy;
+        }
+        lu_solve(cx, base, rhs);
+        if (phase == 1) {
+            const double denom = fmin(1.0, dy1 + LB_SMALL);
+            double s2 = 0.0; int big = 0;
+            if (t < N) {
+                if (fabs(dyc[t]) > scale[t] * denom) big = 1;
+                const double q = dyc[t] / scale[t];
+                s2 = q * q;
+            }
+            if (g.any(big, 3)) { cs.theta = 1; ok = false; break; }
+            const double dy2 = sqrt(g.sum(s2, 2));
+            cs.theta = dy2 / denom;
+            if (cs.theta > 1) { ok = false; break; }
+            if (t == 0) CNT(CNT_RHS)++;    // the reference evaluates derivatives(yT) a second time (same value)
+            phase = 2;                     // next pass: regular increment of the same sub-step, f still current
+        } else {
+            phase = 0;
+            ++it;
+        }
+    }
+    if (ok) { if (t < N) yOut[t] = yT[t] + dy[t]; }
+    g.sync();
+    return ok;
+}
+
+__device__ __forceinline__ double seulex_coeff(int k, int l) {
+    const double ratio = (double)c_nSeq[k] / c_nSeq[l];
+    return 1 / (ratio - 1);
+}
+
+// seulex::solve (A.5); y = V0
+__device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, StepState& step, int& attempts) {
+    const int t = g.tid, N = cx->nEqn;
+    const DevOpts& O = cx->O;
+    const int kMaxx = 11;
+    const double stepFactor1 = 0.6, stepFactor2 = 0.93, stepFactor3 = 0.1, stepFactor4 = 4, stepFactor5 = 0.5,
+                 kFactor1 = 0.7, kFactor2 = 0.9;
+    const double absTol = O.absTol, relTol = O.relTol;
+    const double jacRedo = fmin(1e-4, relTol);
+    double *y = VEC(0), *y0 = VEC(4), *scale = VEC(5), *ySeq = VEC(6), *tb = WS(TB);
+    double temp[12], dxOpt[12];
+    temp[0] = LB_GREAT;
+    double dx = step.dxTry;
+    g.sync();
+    if (t < N) { y0[t] = y[t]; scale[t] = absTol + relTol * fabs(y[t]); }
+    dxOpt[0] = fabs(0.1 * dx);
+    if (step.first || step.prevReject) cs.theta = 2.0 * jacRedo;
+    if (step.first) {
+        const double logTol = -log10(relTol + absTol) * 0.6 + 0.5;
+        int kt = (int)logTol;
+        if (kt > kMaxx - 1) kt = kMaxx - 1;
+        if (kt < 1) kt = 1;
+        cs.kTarg = kt;
+    }
+    bool jacUpdated = false;
+    if (cs.theta > jacRedo) { jacobian(cx, base, y, VEC(3)); jacUpdated = true; }
+    int k = 0;
+    double dxNew = fabs(dx);
+    bool firstk = true;
+    while (firstk || step.reject) {
+        dx = step.forward ? dxNew : -dxNew;
+        firstk = false;
+        step.reject = 0;
+        attempts++;
+        if (t == 0) CNT(CNT_ATTEMPTS)++;
+        if (fabs(dx) < LB_VSMALL || attempts > 100000) { cs.fail = LBCHEM_CELL_UNDERFLOW; return; }
+        if (cs.kTarg + 1 > cx->tbRows) { cs.fail = LBCHEM_CELL_MAX_STEPS; return; }   // extrapolation table too small for this order
+        double errOld = 0;
+#pragma unroll 1
+        for (k = 0; k <= cs.kTarg + 1; ++k) {
+            const bool success = seul(g, cx, base, cs, dx, k);
+            if (cs.fail) return;
+            if (!success) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
+            double s = 0.0;
+            if (t < N) {
+                if (k == 0) y[t] = ySeq[t];
+                else {
+                    tb[(k - 1) * N + t] = ySeq[t];
+                    for (int j = k - 1; j > 0; --j)
+                        tb[(j - 1) * N + t] = tb[j * N + t] + seulex_coeff(k, j) * (tb[j * N + t] - tb[(j - 1) * N + t]);
+                    const double yi = tb[t] + seulex_coeff(k, 0) * (tb[t] - y[t]);
+                    y[t] = yi;
+                    const double sc = absTol + relTol * fabs(y0[t]);
+                    scale[t] = sc;
+                    const double q = (yi - tb[t]) / sc;
+                    s = q * q;
+                }
+            }
+            if (k != 0) {
+                const double err = sqrt(g.sum(s, 1) / N);
+                if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
+                if (err > 1 / LB_SMALL || (k > 1 && err >= errOld)) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
+                errOld = fmin(4 * err, 1.0);
+                const double expo = 1.0 / (k + 1);
+                const double facmin = pow(stepFactor3, expo);
+                double fac;
+                if (err == 0) fac = 1 / facmin;
+                else {
+                    fac = stepFactor2 / pow(err / stepFactor1, expo);
+                    fac = fmax(facmin / stepFactor4, fmin(1 / facmin, fac));
+                }
+                dxOpt[k] = fabs(dx * fac);
+                temp[k] = c_cpu[k] / dxOpt[k];
+                if ((step.first || step.last) && err <= 1) break;
+                if (k == cs.kTarg - 1 && !step.prevReject && !step.first && !step.last) {
+                    if (err <= 1) break;
+                    else if (err > c_nSeq[cs.kTarg] * c_nSeq[cs.kTarg + 1] * 4) {
+                        step.reject = 1;
+                        cs.kTarg = k;
+                        if (cs.kTarg > 1 && temp[k - 1] < kFactor1 * temp[k]) cs.kTarg--;
+                        dxNew = dxOpt[cs.kTarg];
+                        break;
+                    }
+                }
+                if (k == cs.kTarg) {
+                    if (err <= 1) break;
+                    else if (err > c_nSeq[k + 1] * 2) {
+                        step.reject = 1;
+                        if (cs.kTarg > 1 && temp[k - 1] < kFactor1 * temp[k]) cs.kTarg--;
+                        dxNew = dxOpt[cs.kTarg];
+                        break;
+                    }
+                }
+                if (k == cs.kTarg + 1) {
+                    if (err > 1) {
+                        step.reject = 1;
+                        if (cs.kTarg > 1 && temp[cs.kTarg - 1] < kFactor1 * temp[cs.kTarg]) cs.kTarg--;
+                        dxNew = dxOpt[cs.kTarg];
+                    }
+                    break;
+                }
+            }
+        }
+        if (step.reject) {
+            step.prevReject = 1;
+            if (!jacUpdated) {
+                cs.theta = 2.0 * jacRedo;
+                if (cs.theta > jacRedo && !jacUpdated) { jacobian(cx, base, y, VEC(3)); jacUpdated = true; }
+            }
+        }
+    }
+    step.dxDid = dx;
+    x += dx;
+    int kopt;
+    if (k == 1) kopt = 2;
+    else if (k <= cs.kTarg) {
+        kopt = k;
+        if (temp[k - 1] < kFactor1 * temp[k]) kopt = k - 1;
+        else if (temp[k] < kFactor2 * temp[k - 1]) kopt = (k + 1 < kMaxx - 1) ? k + 1 : kMaxx - 1;
+    } else {
+        kopt = k - 1;
+        if (k > 2 && temp[k - 2] < kFactor1 * temp[k - 1]) kopt = k - 2;
+        if (temp[k] < kFactor2 * temp[kopt]) kopt = (k < kMaxx - 1) ? k : kMaxx - 1;
+    }
+    if (step.prevReject) {
+        cs.kTarg = (kopt < k) ? kopt : k;
+        dxNew = fmin(fabs(dx), dxOpt[cs.kTarg]);
+        step.prevReject = 0;
+    } else {
+        if (kopt <= k) dxNew = dxOpt[kopt];
+        else {
+            if (k < cs.kTarg && temp[k] < kFactor2 * temp[k - 1]) dxNew = dxOpt[k] * c_cpu[kopt + 1] / c_cpu[k];
+            else dxNew = dxOpt[k] * c_cpu[kopt] / c_cpu[k];
+        }
+        cs.kTarg = kopt;
+    }
+    step.dxTry = step.forward ? dxNew : -dxNew;
+}
+
+// ODESolver::solve (A.2); y = V0
+template <int SOLVER>
+__device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double xStart, double xEnd, double& dxTry) {
+    StepState step = {1, 1, 0, 0, 0, dxTry, 0.0};
+    double x = xStart;
+    int attempts = 0;
+#pragma unroll 1
+    for (int nStep = 0; nStep < cx->O.maxSteps; ++nStep) {
+        const double dxTry0 = step.dxTry;
+        step.reject = 0;
+        if ((x + step.dxTry - xEnd) * (x + step.dxTry - xStart) > 0) {
+            step.last = 1;
+            step.dxTry = xEnd - x;
+        }
+        if (SOLVER == LBCHEM_SOLVER_SEULEX) {
+            seulex_solve(g, cx, base, cs, x, step, attempts);
+        } else {
+            const double x0 = x;
+            adaptive_solve(g, cx, base, cs, x, step.dxTry);
+            step.dxDid = x - x0;
+        }
+        if (cs.fail) return;
+        if (g.tid == 0) CNT(CNT_STEPS)++;
+        if ((x - xEnd) * (xEnd - xStart) >= 0) {
+            if (nStep > 0 && step.last) step.dxTry = dxTry0;
+            dxTry = step.dxTry;
+            return;
+        }
+        step.first = 0;
+        if (step.reject) step.prevReject = 1;
+    }
+    cs.fail = LBCHEM_CELL_MAX_STEPS;
+}
+
+
+// smem layout: [Ctx (padded to 512 B)] [mechanism blob] [groups x workspace]
+constexpr int CTX_BYTES = 512;
+static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
+
+template <int SOLVER>
+__global__ void __launch_bounds__(TPC * 4, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
+    extern __shared__ double smem[];
+    unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
+    {
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(M.blob);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(sm + CTX_BYTES);
+        for (int i = threadIdx.x; i < M.blobBytes / 8; i += blockDim.x) dst[i] = src[i];
+    }
+    Ctx* cxw = reinterpret_cast<Ctx*>(sm);
+    if (threadIdx.x == 0) {
+        bind(cxw->S, M, sm + CTX_BYTES);
+        cxw->O = O; cxw->O.solver = SOLVER;
+        cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
+        cxw->wsDoubles = ctx_layout(*cxw, M);
+        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN;
+    }
+    __syncthreads();
+    const Ctx* cx = cxw;
+    double* base = reinterpret_cast<double*>(sm + CTX_BYTES + M.blobBytes) + (size_t)(threadIdx.x / TPC) * wsDoubles;
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid;
+    unsigned long long st[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+
+    for (;;) {
+        g.sync();
+        if (t == 0) reinterpret_cast<unsigned long long*>(WS(XS))[0] = atomicAdd(B.queue, 1ull);
+        g.sync();
+        const unsigned long long q = reinterpret_cast<unsigned long long*>(WS(XS))[0];
+        if (q >= (unsigned long long)B.n) break;
+        const long long cell = B.order ? (long long)B.order[q] : (long long)q;
+        const double T0 = B.T[cell];
+        const double p0 = B.p[cell];
+        const double rho = B.rho[cell];
+        const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
+        double dtChem = B.deltaTChem[cell];
+        if (t < CNT_N) CNT(t) = 0;
+        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1;
+        int status;
+        double Tend = T0;
+        double* y = VEC(0);
+        if (T0 > O.Treact) {
+            if (t < nSp) y[t] = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t];
+            if (t == nSp) y[nSp] = T0;
+            if (t == nSp + 1) y[nSp + 1] = p0;
+            g.sync();
+            double timeLeft = deltaT;
+            while (timeLeft > LB_SMALL) {
+                double dt = timeLeft;
+                ode_solve<SOLVER>(g, cx, base, cs, 0.0, dt, dtChem);
+                g.sync();
+                if (t < nSp) y[t] = fmax(0.0, y[t]);
+                g.sync();
+                if (cs.fail) break;
+                timeLeft -= dt;
+            }
+            dtChem = fmin(dtChem, O.deltaTChemMax);
+            if (t < nSp) {
+                const double c0 = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t];
+                B.RR[(size_t)t * B.ldy + cell] = (y[t] - c0) * S.W[t] / deltaT;
+            }
+            Tend = y[nSp];
+            status = cs.fail ? cs.fail : LBCHEM_CELL_OK;
+        } else {
+            if (t < nSp) B.RR[(size_t)t * B.ldy + cell] = 0.0;
+            status = LBCHEM_CELL_SKIPPED;
+        }
+        if (t == 0) {
+            B.deltaTChem[cell] = dtChem;
+            if (B.Tout) B.Tout[cell] = Tend;
+            if (B.cost) B.cost[cell] = (double)CNT(CNT_ATTEMPTS);
+            if (B.status) B.status[cell] = status;
+            st[0] += CNT(CNT_STEPS); st[1] += CNT(CNT_ATTEMPTS); st[2] += CNT(CNT_JAC); st[3] += CNT(CNT_LU);
+            st[4] += CNT(CNT_SOLVE); st[5] += CNT(CNT_RHS); st[6] += (status >= LBCHEM_CELL_MAX_STEPS); st[7] += 1;
+        }
+    }
+    if (t == 0 && st[7]) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) atomicAdd(B.stats + i, st[i]);
+    }
+}
+
+}  // namespace v3
+
+// ------------------------------------------------------------------------------------------------
+// host side: workspace size (must match v3::ctx_layout), configuration, launch
+// ------------------------------------------------------------------------------------------------
+int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol) {
+    int tb = 0;
+    if (solver == LBCHEM_SOLVER_SEULEX) {
+        int kt = (int)(-log10(relTol + absTol) * 0.6 + 0.5);
+        kt = kt < 1 ? 1 : (kt > 10 ? 10 : kt);
+        tb = kt + 4 < 11 ? kt + 4 : 11;
+    }
+    M.tbRows = tb;
+    v3::Ctx c;
+    return v3::ctx_layout(c, M);
+}
+
+bool lb_v3_supported(const V2Mech& M) { return M.nEqn <= v3::TPC && M.nEqn >= 3; }
+int lb_v3_ctx_bytes() { return v3::CTX_BYTES; }
+
+cudaError_t lb_v3_configure(int solver, size_t smemBytes) {
+    return solver == LBCHEM_SOLVER_SEULEX
+               ? cudaFuncSetAttribute(v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes)
+               : cudaFuncSetAttribute(v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+}
+
+cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
+                         const BatchArgs& B, cudaStream_t s) {
+    if (solver == LBCHEM_SOLVER_SEULEX)
+        v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX><<<grid, groups * v3::TPC, smemBytes, s>>>(M, O, B, wsDoubles);
+    else
+        v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34><<<grid, groups * v3::TPC, smemBytes, s>>>(M, O, B, wsDoubles);
+    return cudaGetLastError();
+}

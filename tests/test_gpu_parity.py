@@ -85,11 +85,17 @@ def test_probes_match_oracle(gri, flame):
     chem.close()
 
 
-@pytest.mark.parametrize("tpc", [0, 64], ids=["fast", "general"])
+@pytest.mark.parametrize("kernel", ["v3", "v2", "general"])
 @pytest.mark.parametrize("solver,rel_tol", [("Rosenbrock34", 1e-2), ("seulex", 1e-1)])
-def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol, tpc):
+def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol, kernel, monkeypatch):
     """All 4000 cells of the reference's flame fixture, both tolerance sets of BASELINE config 3, through the
-    fast kernel (register LU, threads_per_cell = 0) and the general kernel (threads_per_cell = 64)."""
+    compact-code kernel (v3, default), the register-LU kernel (LBCHEM_KERNEL=v2) and the general kernel
+    (threads_per_cell = 64)."""
+    tpc = 64 if kernel == "general" else 0
+    if kernel == "v2":
+        monkeypatch.setenv("LBCHEM_KERNEL", "v2")
+    else:
+        monkeypatch.delenv("LBCHEM_KERNEL", raising=False)
     sel = np.arange(flame["T"].shape[0])
     Y, T, p, rho = _state(gri, flame, sel)
     opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, threads_per_cell=tpc)
