@@ -264,15 +264,27 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
     g.sync();
 }
 
+// dc_i/dt = sum over the reactions of species i of nu * omega. Four interleaved partial sums (terms k, k+1, k+2, k+3
+// of the reference's order), combined as (a0 + a1) + (a2 + a3): the species with > 100 reactions (H, OH, O ...)
+// would otherwise serialise one ~30-cycle dependent FMA per term while the rest of the group waits at the barrier.
 __device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
-    double acc = 0.0;
+    double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     const int e = S.spPtr[i + 1];
+    int k = S.spPtr[i];
 #pragma unroll 1
-    for (int k = S.spPtr[i]; k < e; ++k) {
-        const unsigned u = S.spList[k];
-        acc = fma((double)(int)(signed char)(u >> 16), om[u & 0xffffu], acc);
+    for (; k + 3 < e; k += 4) {
+        const unsigned u0 = S.spList[k], u1 = S.spList[k + 1], u2 = S.spList[k + 2], u3 = S.spList[k + 3];
+        a0 = fma((double)(int)(signed char)(u0 >> 16), om[u0 & 0xffffu], a0);
+        a1 = fma((double)(int)(signed char)(u1 >> 16), om[u1 & 0xffffu], a1);
+        a2 = fma((double)(int)(signed char)(u2 >> 16), om[u2 & 0xffffu], a2);
+        a3 = fma((double)(int)(signed char)(u3 >> 16), om[u3 & 0xffffu], a3);
     }
-    return acc;
+#pragma unroll 1
+    for (; k < e; ++k) {
+        const unsigned u = S.spList[k];
+        a0 = fma((double)(int)(signed char)(u >> 16), om[u & 0xffffu], a0);
+    }
+    return (a0 + a1) + (a2 + a3);
 }
 
 // StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
@@ -421,9 +433,19 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
             if (pos == j) pos = ppos;
             const double l = piv * rd;
             row[j] = l;
-            const double* prow = A + ptid * lda;
-#pragma unroll 2
-            for (int k = j + 1; k <= nSp; ++k) row[k] = fma(-l, prow[k], row[k]);
+            const double* __restrict__ prow = A + ptid * lda;
+            double* __restrict__ mine = row;
+            int k = j + 1;
+            // batches of four: all loads first, so the stores of one batch never wait behind its loads
+#pragma unroll 1
+            for (; k + 3 <= nSp; k += 4) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double r0 = mine[k], r1 = mine[k + 1], r2 = mine[k + 2], r3 = mine[k + 3];
+                mine[k] = fma(-l, p0, r0); mine[k + 1] = fma(-l, p1, r1);
+                mine[k + 2] = fma(-l, p2, r2); mine[k + 3] = fma(-l, p3, r3);
+            }
+#pragma unroll 1
+            for (; k <= nSp; ++k) mine[k] = fma(-l, prow[k], mine[k]);
         }
     }
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
