@@ -202,40 +202,48 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     if (entCol.empty()) entCol.push_back(0);
     M.oEntCol = B.add(entCol);
 
-    // deal entries to the 64 threads in contiguous runs balanced by term count
-    std::vector<int> thrEnt(V2_TPC + 1, nEnt), thrN(V2_TPC, 0);
-    {
-        double total = 0; for (int c : entTerms) total += c + 1.0;
-        double acc = 0; int t = 0; thrEnt[0] = 0;
-        for (int e = 0; e < nEnt; ++e) {
-            while (t + 1 < V2_TPC && acc >= total * (t + 1) / V2_TPC) thrEnt[++t] = e;
-            acc += entTerms[e] + 1.0;
-        }
-        while (t + 1 <= V2_TPC) thrEnt[++t] = nEnt;
-    }
-    std::vector<std::vector<unsigned long long>> perThr(V2_TPC);
-    {
-        int e = 0;
-        for (auto& kv : E) {
-            int t = 0; while (!(e >= thrEnt[t] && e < thrEnt[t + 1])) ++t;
-            for (size_t q = 0; q < kv.second.size(); ++q) {
-                const Term& u = kv.second[q];
-                unsigned long long w = (unsigned long long)u.kidx | ((unsigned long long)u.s[0] << 16) | ((unsigned long long)u.s[1] << 24) |
-                                       ((unsigned long long)u.s[2] << 32) | ((unsigned long long)(uint8_t)(int8_t)u.coef << 40);
-                if (q + 1 == kv.second.size()) w |= 1ull << 48;
-                perThr[t].push_back(w);
+    // deal entries to `tpc` threads in contiguous runs balanced by term count; program word k of thread t at [k*tpc + t]
+    struct Prog { std::vector<unsigned long long> jterm; std::vector<int> thrEnt, thrN; int maxT; };
+    auto deal = [&](int tpc) {
+        Prog P;
+        std::vector<int> thrEnt(tpc + 1, nEnt), thrN(tpc, 0);
+        {
+            double total = 0; for (int c : entTerms) total += c + 1.0;
+            double acc = 0; int t = 0; thrEnt[0] = 0;
+            for (int e = 0; e < nEnt; ++e) {
+                while (t + 1 < tpc && acc >= total * (t + 1) / tpc) thrEnt[++t] = e;
+                acc += entTerms[e] + 1.0;
             }
-            ++e;
+            while (t + 1 <= tpc) thrEnt[++t] = nEnt;
         }
-    }
-    int maxT = 1;
-    for (int t = 0; t < V2_TPC; ++t) { thrN[t] = (int)perThr[t].size(); maxT = std::max(maxT, thrN[t]); }
-    std::vector<unsigned long long> jterm((size_t)maxT * V2_TPC, 0ull);
-    for (int t = 0; t < V2_TPC; ++t)
-        for (int k = 0; k < thrN[t]; ++k) jterm[(size_t)k * V2_TPC + t] = perThr[t][k];
-    M.jMaxTerms = maxT;
-    M.blobBytes = (int)B.b.size();
+        std::vector<std::vector<unsigned long long>> perThr(tpc);
+        {
+            int e = 0;
+            for (auto& kv : E) {
+                int t = 0; while (!(e >= thrEnt[t] && e < thrEnt[t + 1])) ++t;
+                for (size_t q = 0; q < kv.second.size(); ++q) {
+                    const Term& u = kv.second[q];
+                    unsigned long long w = (unsigned long long)u.kidx | ((unsigned long long)u.s[0] << 16) | ((unsigned long long)u.s[1] << 24) |
+                                           ((unsigned long long)u.s[2] << 32) | ((unsigned long long)(uint8_t)(int8_t)u.coef << 40);
+                    if (q + 1 == kv.second.size()) w |= 1ull << 48;
+                    perThr[t].push_back(w);
+                }
+                ++e;
+            }
+        }
+        int maxT = 1;
+        for (int t = 0; t < tpc; ++t) { thrN[t] = (int)perThr[t].size(); maxT = std::max(maxT, thrN[t]); }
+        std::vector<unsigned long long> jterm((size_t)maxT * tpc, 0ull);
+        for (int t = 0; t < tpc; ++t)
+            for (int k = 0; k < thrN[t]; ++k) jterm[(size_t)k * tpc + t] = perThr[t][k];
 
+
+        P.jterm = jterm; P.thrEnt = thrEnt; P.thrN = thrN; P.maxT = maxT;
+        return P;
+    };
+    Prog P64 = deal(V2_TPC), P128 = deal(128);
+    M.jMaxTerms = P64.maxT;
+    M.blobBytes = (int)B.b.size();
     auto up = [&](const void* src, size_t bytes, const void** dst) -> bool {
         void* d = nullptr;
         if (cudaMalloc(&d, bytes ? bytes : 8) != cudaSuccess) return false;
@@ -244,9 +252,11 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         *dst = d;
         return true;
     };
-    const void *dBlob, *dTerm, *dEnt, *dN;
-    if (!up(B.b.data(), B.b.size(), &dBlob) || !up(jterm.data(), jterm.size() * 8, &dTerm) ||
-        !up(thrEnt.data(), thrEnt.size() * 4, &dEnt) || !up(thrN.data(), thrN.size() * 4, &dN)) {
+    const void *dBlob, *dTerm, *dEnt, *dN, *dTerm3, *dEnt3, *dN3;
+    if (!up(B.b.data(), B.b.size(), &dBlob) || !up(P64.jterm.data(), P64.jterm.size() * 8, &dTerm) ||
+        !up(P64.thrEnt.data(), P64.thrEnt.size() * 4, &dEnt) || !up(P64.thrN.data(), P64.thrN.size() * 4, &dN) ||
+        !up(P128.jterm.data(), P128.jterm.size() * 8, &dTerm3) || !up(P128.thrEnt.data(), P128.thrEnt.size() * 4, &dEnt3) ||
+        !up(P128.thrN.data(), P128.thrN.size() * 4, &dN3)) {
         err = "cudaMalloc/cudaMemcpy failed while uploading the packed mechanism";
         return LBCHEM_E_CUDA;
     }
@@ -254,6 +264,9 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     M.jterm = static_cast<const unsigned long long*>(dTerm);
     M.jthrEnt = static_cast<const int*>(dEnt);
     M.jthrN = static_cast<const int*>(dN);
+    M.jterm3 = static_cast<const unsigned long long*>(dTerm3);
+    M.jthrEnt3 = static_cast<const int*>(dEnt3);
+    M.jthrN3 = static_cast<const int*>(dN3);
     *out = M;
     return 0;
 }
