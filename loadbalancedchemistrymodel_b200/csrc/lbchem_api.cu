@@ -21,6 +21,7 @@ cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
 int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
 bool lb_v3_supported(const V2Mech& M);
 int lb_v3_ctx_bytes();
+void lb_v3_timing(unsigned long long out[8], bool reset);
 cudaError_t lb_v3_configure(int solver, size_t smemBytes);
 cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s);
@@ -72,6 +73,7 @@ struct lbchem_handle_t {
     V2Mech V2{};                     // packed mechanism of the fast path
     bool v2Built = false, useV2 = false, useV3 = false;
     int v3Groups = 0, v3Ws = 0; size_t v3Smem = 0;
+    double* dScratch = nullptr; int scratchStride = 0; size_t scratchCap = 0;
     int v2Groups = 0; size_t v2Smem = 0;
     double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
     void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
@@ -270,9 +272,17 @@ int configure_v2(lbchem_handle h) {
         const size_t per3 = (size_t)ws * sizeof(double);
         const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.blobBytes;
         if (fixed + per3 <= h->smemMax) {
-            int groups = (int)std::min<size_t>(4, (h->smemMax - fixed) / per3);
+            int groups = (int)std::min<size_t>(6, (h->smemMax - fixed) / per3);
             if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
             h->v3Groups = groups; h->v3Ws = ws;
+            h->scratchStride = (h->V2.nEnt + 11 * h->V2.nEqn + 1) & ~1;
+            const size_t need = (size_t)h->nSM * groups * h->scratchStride * sizeof(double);
+            if (need > h->scratchCap) {
+                if (h->dScratch) cudaFree(h->dScratch);
+                h->dScratch = nullptr; h->scratchCap = 0;
+                CK(cudaMalloc(&h->dScratch, need));
+                h->scratchCap = need;
+            }
             h->v3Smem = fixed + per3 * groups;
             CK(lb_v3_configure(o.solver, h->v3Smem));
             h->useV3 = true;
@@ -395,6 +405,7 @@ int lbchem_destroy(lbchem_handle h) {
     for (void* p : h->allocs) cudaFree(p);
     if (h->dQueue) cudaFree(h->dQueue);
     if (h->dStats) cudaFree(h->dStats);
+    if (h->dScratch) cudaFree(h->dScratch);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     for (Slot& s : h->slots) {
@@ -433,7 +444,7 @@ static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, 
     BatchArgs B;
     B.n = n; B.ldy = ldy; B.Y = Y; B.T = T; B.p = p; B.rho = rho; B.deltaT = deltaT; B.deltaTUniform = deltaT_uniform;
     B.deltaTChem = deltaTChem; B.RR = RR; B.Tout = Tout; B.cost = cost; B.status = status; B.order = nullptr;
-    B.queue = queue; B.stats = h->dStats;
+    B.queue = queue; B.stats = h->dStats; B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
     CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
     if (h->useV3) {
         long long grid3 = h->nSM;
@@ -567,6 +578,12 @@ int lbchem_get_stats(lbchem_handle h, lbchem_stats* out) {
     out->n_steps = st[0]; out->n_attempts = st[1]; out->n_jac = st[2]; out->n_lu = st[3]; out->n_solve = st[4];
     out->n_rhs = st[5]; out->n_failed = st[6]; out->n_cells = st[7];
     out->kernel_ms = ms; out->kernel_launches = h->launches;
+    if (getenv("LBCHEM_TIMING")) {      // debug builds with -DV3_TIMING only
+        unsigned long long tm[8]; lb_v3_timing(tm, true);
+        const double c = st[7] ? (double)st[7] : 1.0;
+        fprintf(stderr, "[v3 timing] cycles per cell: derivatives %.0f jacobian %.0f lu_factor %.0f lu_solve %.0f | LU: update(not-done) %.0f search %.0f barrier %.0f select %.0f  (calls per cell: rhs %.1f jac %.1f lu %.1f solve %.1f)\n",
+                tm[0] / c, tm[1] / c, tm[2] / c, tm[3] / c, tm[4] / c, tm[5] / c, tm[6] / c, tm[7] / c, st[5] / c, st[2] / c, st[3] / c, st[4] / c);
+    }
     return LBCHEM_OK;
 }
 

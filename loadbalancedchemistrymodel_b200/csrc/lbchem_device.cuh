@@ -68,6 +68,8 @@ struct BatchArgs {
     const int* order;            // optional processing order (descending last cost), may be null
     unsigned long long* queue;   // work-queue head
     unsigned long long* stats;   // 8 counters: steps, attempts, jac, lu, solve, rhs, failed, cells
+    double* scratch;             // v3 kernel: per-group global scratch (sparse Jacobian + seulex table), L2-resident
+    int scratchStride;           // doubles per group
 };
 
 // probe kinds (test hooks that run the same device functions as the integrator)

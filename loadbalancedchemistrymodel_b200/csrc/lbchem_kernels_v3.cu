@@ -21,8 +21,7 @@
 
 namespace v3 {
 
-constexpr int TPC = 128;     // threads per cell: 4 warps
-constexpr int HALF = 64;     // threads 0..63 own the matrix rows; threads 64..127 share the row updates
+constexpr int TPC = 64;
 
 struct SMech {            // typed views into the staged blob
     int nSp, nR, nEff;
@@ -49,33 +48,30 @@ __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned c
 // Group-level helpers. Threads derive their coordinates from threadIdx; nothing lives in local memory, so the
 // heavy routines below can be real (non-inlined) functions with exactly one copy in the instruction stream.
 struct Grp {
-    int tid, gid, lane, warp, half, r;
-    double* red;      // 64 doubles of exchange scratch at the start of the group's workspace: 4 slots of 16
+    int tid, gid, lane, warp;
+    double* red;      // 32 doubles of exchange scratch at the start of the group's workspace: 4 slots of 8
     __device__ __forceinline__ Grp(double* base) {
-        tid = threadIdx.x % TPC; gid = threadIdx.x / TPC; lane = threadIdx.x & 31; warp = tid >> 5; half = tid >> 6; r = tid & 63;
-        red = base;
+        tid = threadIdx.x % TPC; gid = threadIdx.x / TPC; lane = threadIdx.x & 31; warp = tid >> 5; red = base;
     }
     __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory"); }
-    // barrier among threads 0..63 of the group only (triangular solves); ids 5..8
-    __device__ __forceinline__ void sync_rows() const { asm volatile("bar.sync %0, %1;" ::"r"(gid + 5), "r"(HALF) : "memory"); }
     // Reductions write slot `s` (0..3). Two reductions with no barrier in between must use different slots.
     __device__ __forceinline__ void sum3(double& a, double& b, double& c, int s) const {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) {
             a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); c += __shfl_xor_sync(0xffffffffu, c, o);
         }
-        double* q = red + 16 * s;
-        if (lane == 0) { q[warp * 3] = a; q[warp * 3 + 1] = b; q[warp * 3 + 2] = c; }
+        double* r = red + 8 * s;
+        if (lane == 0) { r[warp * 3] = a; r[warp * 3 + 1] = b; r[warp * 3 + 2] = c; }
         sync();
-        a = (q[0] + q[3]) + (q[6] + q[9]); b = (q[1] + q[4]) + (q[7] + q[10]); c = (q[2] + q[5]) + (q[8] + q[11]);
+        a = r[0] + r[3]; b = r[1] + r[4]; c = r[2] + r[5];
     }
     __device__ __forceinline__ double sum(double a, int s) const {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-        double* q = red + 16 * s;
-        if (lane == 0) q[warp] = a;
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a;
         sync();
-        return (q[0] + q[1]) + (q[2] + q[3]);
+        return r[0] + r[1];
     }
     __device__ __forceinline__ double maxnan(double v, int s) const {   // max with NaN propagation
         double bad = (v != v) ? 1.0 : 0.0;
@@ -84,18 +80,18 @@ struct Grp {
         for (int o = 16; o > 0; o >>= 1) {
             v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o)); bad = fmax(bad, __shfl_xor_sync(0xffffffffu, bad, o));
         }
-        double* q = red + 16 * s;
-        if (lane == 0) { q[warp * 2] = v; q[warp * 2 + 1] = bad; }
+        double* r = red + 8 * s;
+        if (lane == 0) { r[warp * 2] = v; r[warp * 2 + 1] = bad; }
         sync();
-        v = fmax(fmax(q[0], q[2]), fmax(q[4], q[6])); bad = fmax(fmax(q[1], q[3]), fmax(q[5], q[7]));
+        v = fmax(r[0], r[2]); bad = fmax(r[1], r[3]);
         return bad > 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : v;
     }
     __device__ __forceinline__ int any(int p, int s) const {
         const int a = __any_sync(0xffffffffu, p);
-        double* q = red + 16 * s;
-        if (lane == 0) q[warp] = a ? 1.0 : 0.0;
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a ? 1.0 : 0.0;
         sync();
-        return ((q[0] + q[1]) + (q[2] + q[3])) > 0.0;
+        return (r[0] + r[1]) > 0.0;
     }
 };
 
@@ -105,28 +101,30 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oTB, oCC, oGL, oGH, oME, oOM, oE2, oJS, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oPV, oPART, oA;
+    int oV, oCC, oGL, oGH, oME, oOM, oE2, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA;
     const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
+    double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
 enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N };
 
 __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
-    int p = 64;                               // reduction scratch
+    int p = 32;                               // reduction scratch
     c.oXCH = p; p += 16; c.oXS = p; p += 16; c.oCNT = p; p += 4;
     c.oV = p; p += 10 * N;
-    c.oTB = p; p += M.tbRows * N;
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
-    c.oOM = p; p += M.nR; c.oE2 = p; p += M.nR; c.oJS = p; p += M.nEnt; c.oJT = p; p += M.nSp;
-    c.oRD = p; p += N; c.oSTEP = p; p += (N + 1) / 2;
-    // PV (LU), BS (solves) and PART (gathers) are only live while no reaction sweep runs: they alias E2 when it is big enough
-    if (M.nR >= 2 * HALF + N + M.nSp + 1) { c.oPV = c.oE2; c.oBS = c.oPV + 2 * HALF; c.oPART = c.oBS + N; }
-    else { c.oPV = p; p += 2 * HALF; c.oBS = p; p += N; c.oPART = p; p += M.nSp + 1; }
+    c.oOM = p; p += M.nR; c.oE2 = p; p += M.nR; c.oJT = p; p += M.nSp;
+    c.oRD = p; p += N;
+    if (M.nR >= N) c.oBS = c.oE2; else { c.oBS = p; p += N; }   // BS (solves) is never live during a reaction sweep
+    c.oSTEP = p; p += (N + 1) / 2;
     c.lda = (M.nSp + 1) | 1;                  // odd leading dimension: conflict-free column access across rows
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
     return (p + 1) & ~1;
 }
 #define WS(name) (base + cx->o##name)
+// global scratch of this group: [nEnt] sparse Jacobian JS, then [tbRows x nEqn] seulex extrapolation table
+#define GS_JS (cx->scratch + (size_t)(blockIdx.x * cx->groups + threadIdx.x / TPC) * cx->scratchStride)
+#define GS_TB (GS_JS + cx->nEnt)
 #define VEC(i) (base + cx->oV + (i) * cx->nEqn)
 
 // ---- janaf polynomials (Horner forms identical to the oracle) -----------------------------------
@@ -161,9 +159,7 @@ __device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* bas
     if (t < nSp) {
         if (clamp) { const double c = fmax(y[t], 0.0); CC[t] = c; cs = c; }
         WS(GL)[t] = jha(S.haLo + t, nSp, T) - T * js(S.sLo + t, nSp, T, lnT);
-    } else if (g.half == 1 && g.r < nSp) {
-        const int i = g.r;
-        WS(GH)[i] = jha(S.haHi + i, nSp, T) - T * js(S.sHi + i, nSp, T, lnT);
+        WS(GH)[t] = jha(S.haHi + t, nSp, T) - T * js(S.sHi + t, nSp, T, lnT);
     }
     if (clamp) {
         if (t == nSp) CC[nSp] = 1.0;
@@ -276,13 +272,10 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
 // dc_i/dt = sum over the reactions of species i of nu * omega. Four interleaved partial sums (terms k, k+1, k+2, k+3
 // of the reference's order), combined as (a0 + a1) + (a2 + a3): the species with > 100 reactions (H, OH, O ...)
 // would otherwise serialise one ~30-cycle dependent FMA per term while the rest of the group waits at the barrier.
-// Threads i and 64 + i each take one half of the list of species i (`half`); the caller adds the two parts.
-__device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i, int half) {
+__device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    const int s0 = S.spPtr[i], e0 = S.spPtr[i + 1];
-    const int mid = s0 + ((e0 - s0 + 1) >> 1);
-    const int e = half ? e0 : mid;
-    int k = half ? mid : s0;
+    const int e = S.spPtr[i + 1];
+    int k = S.spPtr[i];
 #pragma unroll 1
     for (; k + 3 < e; k += 4) {
         const unsigned u0 = S.spList[k], u1 = S.spList[k + 1], u2 = S.spList[k + 2], u3 = S.spList[k + 3];
@@ -311,12 +304,8 @@ __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const doub
     reaction_sweep(cx, base, 0, T, lnT, invT);
     const double RR = cx->O.RR;
     double rho = 0.0, cp = 0.0, dT = 0.0;
-    double dpart = 0.0;
-    if (g.r < nSp) dpart = gather_species(S, WS(OM), g.r, g.half);
-    if (g.half == 1 && g.r < nSp) WS(PART)[g.r] = dpart;
-    g.sync();
     if (t < nSp) {
-        const double d = dpart + WS(PART)[t];
+        const double d = gather_species(S, WS(OM), t);
         dydt[t] = d;
         const double ci = WS(CC)[t];
         const bool lo = T < S.Tc[t];
@@ -347,14 +336,10 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
         const double lnT = log(Tp), invT = 1.0 / Tp;
         prepare(g, cx, base, y, Tp, lnT, pass == 0);
         reaction_sweep(cx, base, pass == 0, Tp, lnT, invT);
-        double dpart = 0.0;
-        if (g.r < nSp && (pass > 0 || cx->O.dfdxIsDcdt)) dpart = gather_species(S, WS(OM), g.r, g.half);
-        if (g.half == 1 && g.r < nSp) WS(PART)[g.r] = dpart;
-        g.sync();
         if (pass == 0) {
-            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? dpart + WS(PART)[t] : 0.0;
+            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? gather_species(S, WS(OM), t) : 0.0;
             // gather program: acc += coef * k * c1 * c2 * c3, entry closed by the `last` flag
-            const double* KFR = WS(A); const double* CC = WS(CC); double* JS = WS(JS);
+            const double* KFR = WS(A); const double* CC = WS(CC); double* JS = GS_JS;
             const int nR = S.nR;
             const int nT = cx->jthrN[t];
             int e = cx->jthrEnt[t];
@@ -363,7 +348,7 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
             unsigned long long wd = nT > 0 ? prog[0] : 0ull;
 #pragma unroll 1
             for (int k = 0; k < nT; ++k) {
-                const unsigned long long nx = (k + 1 < nT) ? prog[(size_t)(k + 1) * TPC] : 0ull;   // prefetch
+                const unsigned long long nx = (k + 1 < nT) ? prog[(size_t)(k + 1) * V2_TPC] : 0ull;   // prefetch
                 const unsigned kid = V2_T_K(wd);
                 const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
                 const double d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
@@ -372,7 +357,7 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
                 wd = nx;
             }
         } else if (t < nSp) {
-            const double d = dpart + WS(PART)[t];
+            const double d = gather_species(S, WS(OM), t);
             if (pass == 1) dp = d; else WS(JT)[t] = 0.5 * (dp - d) / delta;
         }
         g.sync();
@@ -390,24 +375,18 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
 __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const Grp g(base);
     const SMech& S = cx->S;
-    const int nSp = S.nSp, t = g.tid, r = g.r, h = g.half, lda = cx->lda, N = cx->nEqn;
+    const int nSp = S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
     double* A = WS(A);
     double* RD = WS(RD);
     int* STEP = reinterpret_cast<int*>(WS(STEP));
     double* XCH = WS(XCH);
-    double* PV = WS(PV);
-    double* row = A + r * lda;        // threads r and 64 + r work on row r
+    double* row = A + t * lda;
     g.sync();
-    // build: half 0 zero-fills and scatters the first half of the row's entries, half 1 the rest
     double big = fabs(dg);
-    if (r < nSp) {
-        const int mid = (nSp + 1) >> 1;
-#pragma unroll 1
-        for (int k = h ? mid : 0; k < (h ? nSp + 1 : mid); ++k) row[k] = 0.0;
-    }
-    g.sync();
     if (t < nSp) {
-        const double* JS = WS(JS);
+#pragma unroll 1
+        for (int k = 0; k <= nSp; ++k) row[k] = 0.0;
+        const double* JS = GS_JS;
         const int e1 = S.rowPtr[t + 1];
 #pragma unroll 1
         for (int e = S.rowPtr[t]; e < e1; ++e) row[S.entCol[e]] = -JS[e];
@@ -419,36 +398,30 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     }
     if (g.any(t < N && big == 0.0, 2)) return LBCHEM_CELL_SINGULAR;
     const double vv = 1.0 / big;
-    bool done = (r >= nSp);            // both halves track the state of row r
-    int pos = r;
+    bool done = (t >= nSp);
+    int pos = t;
     if (t >= nSp && t < N) { STEP[t] = t; RD[t] = 1.0 / dg; }
 #pragma unroll 1
     for (int j = 0; j < nSp; ++j) {
+        const double piv = done ? 0.0 : row[j];
+        const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+        const bool c1 = hi == mh;
+        const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
+        const bool c2 = c1 && lo == ml;
+        const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
+        const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
+        const bool win = c2 && pp == mp;
         const int par = j & 1;
-        double piv = 0.0;
-        if (h == 0) {
-            // column j of every row was last written by half 0 (it owns column j + 1 of each update), so this
-            // read needs no barrier; half 1 gets the value through PV after the barrier below
-            piv = done ? 0.0 : row[j];
-            PV[par * HALF + r] = piv;
-            const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
-            const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-            const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
-            const bool c1 = hi == mh;
-            const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
-            const bool c2 = c1 && lo == ml;
-            const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
-            const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
-            if (c2 && pp == mp) {
-                double* slot = XCH + (g.warp * 2 + par) * 4;
-                slot[0] = __longlong_as_double((long long)key);
-                reinterpret_cast<int*>(slot + 1)[0] = pos;
-                reinterpret_cast<int*>(slot + 1)[1] = r;
-                slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
-            }
+        if (win) {
+            double* slot = XCH + (g.warp * 2 + par) * 4;
+            slot[0] = __longlong_as_double((long long)key);
+            reinterpret_cast<int*>(slot + 1)[0] = pos;
+            reinterpret_cast<int*>(slot + 1)[1] = t;
+            slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
         }
         g.sync();
-        if (h == 1) piv = PV[par * HALF + r];
         const double* s0 = XCH + (0 * 2 + par) * 4;
         const double* s1 = XCH + (1 * 2 + par) * 4;
         const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
@@ -456,31 +429,28 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
         const double* sw = (k1 > k0 || (k1 == k0 && p1 > p0)) ? s1 : s0;
         const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
-        const int prow_id = reinterpret_cast<const int*>(sw + 1)[1];
+        const int ptid = reinterpret_cast<const int*>(sw + 1)[1];
         const double rd = sw[2];
-        if (r == prow_id) {
-            done = true;
-            if (h == 0) { STEP[r] = j; RD[j] = rd; if (piv == 0.0) row[j] = LB_SMALL; }
+        if (t == ptid) {
+            done = true; STEP[t] = j; RD[j] = rd;
+            if (piv == 0.0) row[j] = LB_SMALL;
         } else if (!done) {
             if (pos == j) pos = ppos;
             const double l = piv * rd;
-            if (h == 0) row[j] = l;
-            const double* __restrict__ prow = A + prow_id * lda;
+            row[j] = l;
+            const double* __restrict__ prow = A + ptid * lda;
             double* __restrict__ mine = row;
-            // columns j+1 .. nSp: half 0 takes the first part (always including j + 1, the next pivot column)
-            const int cnt = nSp - j;                     // columns left
-            const int c0 = (cnt + 1) >> 1;               // half 0's share
-            int k = h ? j + 1 + c0 : j + 1;
-            const int kend = h ? nSp + 1 : j + 1 + c0;   // exclusive
+            int k = j + 1;
+            // batches of four: all loads first, so the stores of one batch never wait behind its loads
 #pragma unroll 1
-            for (; k + 3 < kend; k += 4) {
-                const double q0 = prow[k], q1 = prow[k + 1], q2 = prow[k + 2], q3 = prow[k + 3];
+            for (; k + 3 <= nSp; k += 4) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
                 const double r0 = mine[k], r1 = mine[k + 1], r2 = mine[k + 2], r3 = mine[k + 3];
-                mine[k] = fma(-l, q0, r0); mine[k + 1] = fma(-l, q1, r1);
-                mine[k + 2] = fma(-l, q2, r2); mine[k + 3] = fma(-l, q3, r3);
+                mine[k] = fma(-l, p0, r0); mine[k + 1] = fma(-l, p1, r1);
+                mine[k + 2] = fma(-l, p2, r2); mine[k + 3] = fma(-l, p3, r3);
             }
 #pragma unroll 1
-            for (; k < kend; ++k) mine[k] = fma(-l, prow[k], mine[k]);
+            for (; k <= nSp; ++k) mine[k] = fma(-l, prow[k], mine[k]);
         }
     }
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
@@ -488,40 +458,36 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     return 0;
 }
 
-// x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out).
-// The column recurrences are sequential: only threads 0..63 (one per row) take part, on their own named barrier;
-// the other two warps of the group wait at the closing group barrier.
+// x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out)
 __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     const Grp g(base);
     const int nSp = cx->S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
+    const double* row = WS(A) + t * lda;
+    const double* RD = WS(RD);
+    double* BS = WS(BS);
     g.sync();
-    if (g.half == 0) {
-        const double* row = WS(A) + t * lda;
-        const double* RD = WS(RD);
-        double* BS = WS(BS);
-        const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
-        double bt = t < N ? x[t] : 0.0;
-        const bool sp = t < nSp;
-        // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
+    const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
+    double bt = t < N ? x[t] : 0.0;
+    const bool sp = t < nSp;
+    // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
-        for (int j = 0; j < nSp; ++j) {
-            if (step == j) BS[j] = bt;
-            g.sync_rows();
-            if (sp && step > j) bt = fma(-row[j], BS[j], bt);
-        }
-        // backward substitution: p and T first (diagonal rows), then the species columns in descending order
-        if (t == nSp + 1) x[t] = bt * RD[t];
-        if (t == nSp) { const double v = bt * RD[t]; BS[t] = v; x[t] = v; }
-        g.sync_rows();
-        if (sp) bt = fma(-row[nSp], BS[nSp], bt);
-#pragma unroll 1
-        for (int j = nSp - 1; j >= 0; --j) {
-            if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
-            g.sync_rows();
-            if (sp && step < j) bt = fma(-row[j], BS[j], bt);
-        }
-        if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_SOLVE]++;
+    for (int j = 0; j < nSp; ++j) {
+        if (step == j) BS[j] = bt;
+        g.sync();
+        if (sp && step > j) bt = fma(-row[j], BS[j], bt);
     }
+    // backward substitution: p and T first (diagonal rows), then the species columns in descending order
+    if (t == nSp + 1) x[t] = bt * RD[t];
+    if (t == nSp) { const double v = bt * RD[t]; BS[t] = v; x[t] = v; }
+    g.sync();
+    if (sp) bt = fma(-row[nSp], BS[nSp], bt);
+#pragma unroll 1
+    for (int j = nSp - 1; j >= 0; --j) {
+        if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
+        g.sync();
+        if (sp && step < j) bt = fma(-row[j], BS[j], bt);
+    }
+    if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_SOLVE]++;
     g.sync();
 }
 
@@ -675,7 +641,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
                  kFactor1 = 0.7, kFactor2 = 0.9;
     const double absTol = O.absTol, relTol = O.relTol;
     const double jacRedo = fmin(1e-4, relTol);
-    double *y = VEC(0), *y0 = VEC(4), *scale = VEC(5), *ySeq = VEC(6), *tb = WS(TB);
+    double *y = VEC(0), *y0 = VEC(4), *scale = VEC(5), *ySeq = VEC(6), *tb = GS_TB;
     double temp[12], dxOpt[12];
     temp[0] = LB_GREAT;
     double dx = step.dxTry;
@@ -845,7 +811,7 @@ constexpr int CTX_BYTES = 512;
 static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
 
 template <int SOLVER>
-__global__ void __launch_bounds__(TPC * 4, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
+__global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
     extern __shared__ double smem[];
     unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
     {
@@ -859,7 +825,8 @@ __global__ void __launch_bounds__(TPC * 4, 1) integrate_v3_kernel(V2Mech M, DevO
         cxw->O = O; cxw->O.solver = SOLVER;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
-        cxw->jterm = M.jterm3; cxw->jthrEnt = M.jthrEnt3; cxw->jthrN = M.jthrN3;
+        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN;
+        cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
     }
     __syncthreads();
     const Ctx* cx = cxw;
@@ -961,3 +928,6 @@ cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int
         v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34><<<grid, groups * v3::TPC, smemBytes, s>>>(M, O, B, wsDoubles);
     return cudaGetLastError();
 }
+
+// debug hook kept for API compatibility (phase timing lives in the experimental 128-thread variant)
+void lb_v3_timing(unsigned long long out[8], bool reset) { (void)reset; for (int i = 0; i < 8; ++i) out[i] = 0; }
