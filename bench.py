@@ -25,6 +25,8 @@ from pathlib import Path
 
 import numpy as np
 
+_emit = print
+
 ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
@@ -48,10 +50,10 @@ def parse():
     return ap.parse_args()
 
 
-def make_workload(name, n, rank):
+def make_workload(name, n, rank, world=1):
     from loadbalancedchemistrymodel_b200 import workloads as W
     if name == "gri_skewed":
-        return W.gri_skewed(n, rank=rank)
+        return W.gri_skewed(n, rank=rank, world=world)
     return W.gri_uniform(n, rank=rank)
 
 
@@ -61,7 +63,7 @@ def config_dict(args, n_gpus, extra=None):
         "workload": f"{args.workload}: GRI-Mech 3.0 (53 species, 325 reactions), {args.cells} synthetic cells per GPU "
                     f"(BASELINE config 3; fixture cells T>1500 K resampled + noise, seed 1003)",
         "mechanism": "GRI-3.0", "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
-        "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": f"cells sharded over {n_gpus} GPU(s), no data-path collective",
+        "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; per step: all-gather of the cost, bit-exact plan, NCCL p2p forward/return of planned cells (model.py)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
         "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
     }
     if extra:
@@ -90,7 +92,7 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_sample = args.cpu_sample or min(args.cells, 600 * cores)
+    n_sample = args.cpu_sample or min(args.cells, 1500 * cores)
     rate, dt, _ = cpu_oracle_rate(args, n_sample, cores, steps=args.steps, warmup=args.warmup)
     sample = f"{n_sample} cells of the workload per step, {cores} threads, static contiguous partition"
     line = {
@@ -101,7 +103,7 @@ def run_reference(args):
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "CPU oracle = restatement of the reference's solveCell + OpenFOAM ODE stack (reference needs OpenFOAM; unbuildable here)",
     }
-    print(json.dumps(line))
+    _emit(json.dumps(line))
 
 
 class ClockSampler:
@@ -166,7 +168,7 @@ def run_b200(args):
 
     s, atol, rtol = SOLVERS[args.solver]
     n = args.cells
-    mech, Y, T, p, rho = make_workload(args.workload, n, rank)
+    mech, Y, T, p, rho = make_workload(args.workload, n, rank, world)
     nSp = mech.n_species
     chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol), device=local)
 
@@ -187,15 +189,22 @@ def run_b200(args):
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream().cuda_stream
 
+    from loadbalancedchemistrymodel_b200.model import CudaCellSolver, LoadBalancedChemistryModel
+    cell_solver = CudaCellSolver(chem)
+    model = LoadBalancedChemistryModel(nSp, cell_solver, dev) if world > 1 else None
+    moved = {"sent": 0, "recv": 0}
+
     def step_device():
-        # one LoadBalancedChemistryModel::solve(deltaT): integrate every local cell, sum the per-cell cost,
-        # all-gather it and derive the balancing plan for the next step (reference .C:512-519, :701)
-        dtc.copy_(dtc0)
-        chem.solve_device(n, n, dY, dT_, dp, drho, W.DELTA_T, dtc, dRR, dTout, dcost, dstatus, stream=stream)
-        if world > 1:
-            tot = dcost.sum().reshape(1)
-            dist.all_gather_into_tensor(gathered, tot)
-            capi.balance_plan(gathered.cpu().numpy(), cells_per_rank)
+        # one LoadBalancedChemistryModel::solve(deltaT). N = 1: one kernel over the shard. N > 1: the host driver
+        # (model.py) -- all-gather of the cost, bit-exact plan, cellsToSend scan, NCCL p2p forward trip, own tail then
+        # received cells, return trip, unpack (reference .C:453-704); the first call is its firstTime_ branch.
+        if model is None:
+            dtc.copy_(dtc0)
+            chem.solve_device(n, n, dY, dT_, dp, drho, W.DELTA_T, dtc, dRR, dTout, dcost, dstatus, stream=stream)
+            cell_solver.launches += 1
+        else:
+            model.solve(dY, dT_, dp, drho, W.DELTA_T, dtc0)
+            moved["sent"] = model.last.get("sent_cells", 0); moved["recv"] = model.last.get("recv_cells", 0)
 
     def barrier():
         if world > 1:
@@ -205,6 +214,7 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         step_device()
     barrier()
+    launches0 = cell_solver.launches
     sampler = ClockSampler(local) if rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
@@ -215,6 +225,7 @@ def run_b200(args):
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
+    gpu_launches = cell_solver.launches - launches0
     st = chem.stats()                      # counters + CUDA-event duration of the last integration kernel
     kernel_ms.append(st["kernel_ms"])
     t = torch.tensor([ms], dtype=torch.float64, device=dev)
@@ -265,9 +276,17 @@ def run_b200(args):
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
         hbm_ach = 912.0 * n / (k_ms * 1e-3) / 1e9
+        traffic = None          # dram bytes per launch from the committed ncu --set full capture of this same configuration
+        try:
+            tr = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())
+            key = f"{args.solver}:{n}"
+            if key in tr:
+                traffic = tr[key]["dram_bytes"]
+        except Exception:
+            pass
         roofline = {
-            "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": None,
-            "kernel": "integrate_kernel<64>", "kernel_ms": k_ms,
+            "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
+            "kernel": "v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)", "kernel_ms": k_ms,
             "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
             "flops_per_cell": flops / n, "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts",
             "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
@@ -284,10 +303,11 @@ def run_b200(args):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config_dict(args, world), "clocks": clocks, "e2e": e2e,
-            "gpu_launches": args.steps * 1, "roofline": roofline, "cpu_baseline": cpu,
+            "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu,
             "stats_last_step": {k: int(v) for k, v in st.items() if k.startswith("n_")}, "failed_cells": n_failed,
+            "balance_last_step": ({"rank0_sent_cells": moved["sent"], "rank0_recv_cells": moved["recv"]} if world > 1 else None),
         }
-        print(json.dumps(line))
+        _emit(json.dumps(line))
     chem.close()
     if world > 1:
         dist.destroy_process_group()
@@ -295,6 +315,15 @@ def run_b200(args):
 
 def main():
     args = parse()
+    # Libraries (NCCL's version banner, torchrun notices) may write to stdout; the contract is ONE JSON line there.
+    # Everything but the final line goes to stderr.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    global _emit
+    def _emit(line):
+        sys.stdout.flush()
+        os.write(real_stdout, (line + "\n").encode())
     if args.impl == "reference":
         run_reference(args)
     else:

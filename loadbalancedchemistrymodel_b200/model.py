@@ -35,6 +35,7 @@ class CudaCellSolver:
 
     def __init__(self, chem: "capi.Chemistry"):
         self.chem = chem
+        self.launches = 0
 
     def __call__(self, Y, T, p, rho, deltaT, deltaTChem):
         nSp, n = Y.shape
@@ -46,6 +47,7 @@ class CudaCellSolver:
             assert Y.is_cuda and Y.is_contiguous(), "the CUDA cell solver needs contiguous device tensors"
             stream = torch.cuda.current_stream(Y.device).cuda_stream
             self.chem.solve_device(n, n, Y, T, p, rho, deltaT, deltaTChem, RR, Tout, cost, status, stream=stream)
+            self.launches += 1
         return RR, Tout, cost, status
 
 

@@ -59,9 +59,12 @@ def gri_uniform(n: int, seed: int = 1003, rank: int = 0):
     return mech, Y, T, p, density(mech, Y, T, p)
 
 
-def gri_skewed(n: int, hot_fraction: float = 0.1, seed: int = 1004, rank: int = 0, hot_first: bool = True):
+def gri_skewed(n: int, hot_fraction: float = 0.1, seed: int = 1004, rank: int = 0, hot_first: bool = True, world: int = 1):
     """Config 4: `hot_fraction` of the cells drawn as in config 3, the rest from fixture cells with T < 350 K
-    (1-2 sub-steps); hot cells contiguous at the start of the index space (the flame front sits in few ranks)."""
+    (1-2 sub-steps); hot cells contiguous at the start of the GLOBAL index space (the flame front sits in few ranks):
+    with `world` ranks of n cells each, rank r holds clamp(hot_fraction*world - r, 0, 1) of its cells hot, so at
+    world = 8 rank 0 is 80 % hot and ranks 1..7 are cold."""
+    hot_fraction = min(1.0, max(0.0, hot_fraction * world - rank))
     mech = load_gri()
     T0, p0, Y0 = load_flame()
     hot = np.nonzero(T0 > 1500.0)[0]
