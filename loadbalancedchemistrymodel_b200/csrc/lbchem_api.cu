@@ -270,7 +270,7 @@ int configure_v2(lbchem_handle h) {
     if (!(gen && !strcmp(gen, "v2")) && lb_v3_supported(h->V2)) {
         const int ws = lb_v3_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol);
         const size_t per3 = (size_t)ws * sizeof(double);
-        const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.blobBytes;
+        const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.hotBytes;
         if (fixed + per3 <= h->smemMax) {
             int groups = (int)std::min<size_t>(6, (h->smemMax - fixed) / per3);
             if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
@@ -285,6 +285,9 @@ int configure_v2(lbchem_handle h) {
             }
             h->v3Smem = fixed + per3 * groups;
             CK(lb_v3_configure(o.solver, h->v3Smem));
+            if (getenv("LBCHEM_VERBOSE"))
+                fprintf(stderr, "[lbchem] v3 kernel: %d cells per CTA, %d B workspace per cell, %d B mechanism in smem, %zu B dynamic smem\n",
+                        groups, (int)per3, h->V2.hotBytes, h->v3Smem);
             h->useV3 = true;
             return LBCHEM_OK;
         }

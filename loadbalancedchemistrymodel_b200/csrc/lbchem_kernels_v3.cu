@@ -45,6 +45,15 @@ __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned c
 #undef P
 }
 
+// cp coefficients and the matrix sparsity lists are read once per call by a few threads: they stay in global memory
+// (L2-resident) so that the shared-memory copy of the mechanism is smaller and one more cell fits per SM.
+__device__ __forceinline__ void bind_cold(SMech& S, const V2Mech& M) {
+    if (M.hotBytes >= M.blobBytes) return;
+#define PC(T, off) reinterpret_cast<const T*>(M.blob + M.off)
+    S.cpLo = PC(double, oCpLo); S.cpHi = PC(double, oCpHi); S.rowPtr = PC(int, oRowPtr); S.entCol = PC(unsigned char, oEntCol);
+#undef PC
+}
+
 // Group-level helpers. Threads derive their coordinates from threadIdx; nothing lives in local memory, so the
 // heavy routines below can be real (non-inlined) functions with exactly one copy in the instruction stream.
 struct Grp {
@@ -101,7 +110,7 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oE2, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA;
+    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA;
     const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
@@ -110,14 +119,14 @@ enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N }
 __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
     int p = 32;                               // reduction scratch
-    c.oXCH = p; p += 16; c.oXS = p; p += 16; c.oCNT = p; p += 4;
-    c.oV = p; p += 10 * N;
+    c.oXCH = p; p += 16; c.oXS = p; p += 2; c.oCNT = p; p += 4;
+    c.oV = p; p += 9 * N;
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
-    c.oOM = p; p += M.nR; c.oE2 = p; p += M.nR; c.oJT = p; p += M.nSp;
+    c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
     c.oRD = p; p += N;
-    if (M.nR >= N) c.oBS = c.oE2; else { c.oBS = p; p += N; }   // BS (solves) is never live during a reaction sweep
+    c.oBS = p; p += N;
     c.oSTEP = p; p += (N + 1) / 2;
-    c.lda = (M.nSp + 1) | 1;                  // odd leading dimension: conflict-free column access across rows
+    c.lda = M.nSp + 1;                        // even for GRI (54): column accesses across rows are 2-way conflicted, rows are not
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
     return (p + 1) & ~1;
 }
@@ -180,36 +189,14 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
     const Grp g(base);
     const SMech& S = cx->S;
     const int nR = S.nR, nFall = cx->nFall;
-    double *OM = WS(OM), *E2 = WS(E2);
+    double* OM = WS(OM);
     const double *GL = WS(GL), *GH = WS(GH), *ME = WS(ME), *CC = WS(CC);
-    // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor), E2[p] = exp(-dG/RT) if reversible
+    // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
 #pragma unroll 1
-    for (int i = g.tid; i < 2 * nR; i += TPC) {
-        const bool second = i >= nR;
-        const int p = second ? i - nR : i;
-        const unsigned iw = S.info[p];
-        double arg = 0.0, val = 1.0;
-        bool need;
-        if (!second) {
-            need = V2_HASEXP(iw);
-            if (need) arg = fma(S.beta[p], lnT, -S.Ta[p] * invT);
-        } else {
-            need = false;
-            if (V2_REV(iw)) {
-                const double* G = (T < S.tcTab[V2_TCI(iw)]) ? GL : GH;
-                const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
-                double gs = 0.0;
-#pragma unroll 1
-                for (unsigned s = 0; s < V2_NR(iw); ++s) { const unsigned sl = V2_SLOT(rp, s); gs = fma((double)V2_NU(sl), G[V2_SP(sl)], gs); }
-#pragma unroll 1
-                for (unsigned s = 0; s < V2_NL(iw); ++s) { const unsigned sl = V2_SLOT(lp, s); gs = fma(-(double)V2_NU(sl), G[V2_SP(sl)], gs); }
-                arg = -gs * invT;
-                need = arg < 600.0;
-                val = LB_VGREAT;
-            }
-        }
-        if (need) val = exp(arg);
-        (second ? E2 : OM)[p] = val;
+    for (int p = g.tid; p < nR; p += TPC) {
+        double val = 1.0;
+        if (V2_HASEXP(S.info[p])) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
+        OM[p] = val;
     }
     g.sync();
     // (2) fall-off reactions (sorted last): OM[p] <- blended rate constant
@@ -252,7 +239,15 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
         }
         double kr = 0.0;
         if (V2_REV(iw)) {
-            double Kc = E2[p];
+            const double* G = (T < S.tcTab[V2_TCI(iw)]) ? GL : GH;
+            const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
+            double gs = 0.0;
+#pragma unroll 1
+            for (unsigned s = 0; s < V2_NR(iw); ++s) { const unsigned sl = V2_SLOT(rp, s); gs = fma((double)V2_NU(sl), G[V2_SP(sl)], gs); }
+#pragma unroll 1
+            for (unsigned s = 0; s < V2_NL(iw); ++s) { const unsigned sl = V2_SLOT(lp, s); gs = fma(-(double)V2_NU(sl), G[V2_SP(sl)], gs); }
+            const double arg = -gs * invT;
+            double Kc = (arg < 600.0) ? exp(arg) : LB_VGREAT;
             const int dn = (int)V2_DNC(iw) - 3;
             if (dn != 0) {
                 if (dn == 1) Kc *= x;
@@ -345,16 +340,29 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
             int e = cx->jthrEnt[t];
             double acc = 0.0;
             const unsigned long long* prog = cx->jterm + t;
-            unsigned long long wd = nT > 0 ? prog[0] : 0ull;
+            // the program streams from global memory (L2): fetch eight words ahead so that one L2 round trip is paid per
+            // eight terms instead of per term
+            constexpr int PF = 8;
+            unsigned long long cur[PF], nxt[PF];
+#pragma unroll
+            for (int q = 0; q < PF; ++q) cur[q] = (q < nT) ? prog[(size_t)q * TPC] : 0ull;
 #pragma unroll 1
-            for (int k = 0; k < nT; ++k) {
-                const unsigned long long nx = (k + 1 < nT) ? prog[(size_t)(k + 1) * V2_TPC] : 0ull;   // prefetch
-                const unsigned kid = V2_T_K(wd);
-                const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
-                const double d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
-                acc = fma((double)V2_T_COEF(wd), d, acc);
-                if (V2_T_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
-                wd = nx;
+            for (int k0 = 0; k0 < nT; k0 += PF) {
+#pragma unroll
+                for (int q = 0; q < PF; ++q) nxt[q] = (k0 + PF + q < nT) ? prog[(size_t)(k0 + PF + q) * TPC] : 0ull;
+#pragma unroll
+                for (int q = 0; q < PF; ++q) {
+                    if (k0 + q < nT) {
+                        const unsigned long long wd = cur[q];
+                        const unsigned kid = V2_T_K(wd);
+                        const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
+                        const double d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
+                        acc = fma((double)V2_T_COEF(wd), d, acc);
+                        if (V2_T_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
+                    }
+                }
+#pragma unroll
+                for (int q = 0; q < PF; ++q) cur[q] = nxt[q];
             }
         } else if (t < nSp) {
             const double d = gather_species(S, WS(OM), t);
@@ -578,7 +586,7 @@ __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, 
     const int t = g.tid, N = cx->nEqn;
     const int nSteps = c_nSeq[k];
     const double dx = dxTot / nSteps;
-    double *y0 = VEC(4), *scale = VEC(5), *yOut = VEC(6), *dy = VEC(7), *yT = VEC(1), *f = VEC(8), *dyc = VEC(9);
+    double *y0 = VEC(4), *scale = VEC(5), *yOut = VEC(6), *dy = VEC(7), *yT = VEC(1), *f = VEC(8), *dyc = VEC(2);
     const int st = lu_factor(cx, base, 1 / dx);
     if (st) { cs.fail = st; return false; }
     bool ok = true;
@@ -817,11 +825,12 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
     {
         const unsigned long long* src = reinterpret_cast<const unsigned long long*>(M.blob);
         unsigned long long* dst = reinterpret_cast<unsigned long long*>(sm + CTX_BYTES);
-        for (int i = threadIdx.x; i < M.blobBytes / 8; i += blockDim.x) dst[i] = src[i];
+        for (int i = threadIdx.x; i < M.hotBytes / 8; i += blockDim.x) dst[i] = src[i];
     }
     Ctx* cxw = reinterpret_cast<Ctx*>(sm);
     if (threadIdx.x == 0) {
         bind(cxw->S, M, sm + CTX_BYTES);
+        bind_cold(cxw->S, M);
         cxw->O = O; cxw->O.solver = SOLVER;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
@@ -830,7 +839,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
     }
     __syncthreads();
     const Ctx* cx = cxw;
-    double* base = reinterpret_cast<double*>(sm + CTX_BYTES + M.blobBytes) + (size_t)(threadIdx.x / TPC) * wsDoubles;
+    double* base = reinterpret_cast<double*>(sm + CTX_BYTES + M.hotBytes) + (size_t)(threadIdx.x / TPC) * wsDoubles;
     const Grp g(base);
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid;

@@ -30,6 +30,7 @@
 struct V2Mech {
     int nSp, nR, nEqn, nEff, nFall, nEnt, nTc;
     int blobBytes;
+    int hotBytes;                        // leading part of the blob that the v3 kernel stages in shared memory
     // byte offsets into the blob (all 8-byte aligned)
     int oW, oTc, oCpLo, oCpHi, oHaLo, oHaHi, oSLo, oSHi;
     int oA, oBeta, oTa, oInfo, oLpk, oRpk, oFall, oTcTab;

@@ -115,7 +115,6 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         const int sI[6] = {4, 3, 2, 1, 0, 6};  const double sD[6] = {4, 3, 2, 1, 1, 1};
         M.oW = B.add(std::vector<double>(m->W, m->W + nSp));
         M.oTc = B.add(std::vector<double>(m->Tcommon, m->Tcommon + nSp));
-        M.oCpLo = B.add(soa2(m->janaf_low, nSp, cpI, cpD, 5)); M.oCpHi = B.add(soa2(m->janaf_high, nSp, cpI, cpD, 5));
         M.oHaLo = B.add(soa2(m->janaf_low, nSp, haI, haD, 6)); M.oHaHi = B.add(soa2(m->janaf_high, nSp, haI, haD, 6));
         M.oSLo = B.add(soa2(m->janaf_low, nSp, sI, sD, 6));    M.oSHi = B.add(soa2(m->janaf_high, nSp, sI, sD, 6));
     }
@@ -197,6 +196,12 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
             entTerms.push_back((int)kv.second.size());
         }
         while (row < N) rowPtr[++row] = (int)entCol.size();
+    }
+    // cold tail of the blob (the v3 kernel leaves it in global memory): cp polynomials, matrix sparsity lists
+    M.hotBytes = (int)B.b.size();
+    {
+        const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
+        M.oCpLo = B.add(soa2(m->janaf_low, nSp, cpI, cpD, 5)); M.oCpHi = B.add(soa2(m->janaf_high, nSp, cpI, cpD, 5));
     }
     M.oRowPtr = B.add(rowPtr);
     if (entCol.empty()) entCol.push_back(0);
