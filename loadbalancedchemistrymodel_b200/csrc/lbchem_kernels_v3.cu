@@ -110,7 +110,7 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA;
+    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oPIV, oXCH, oXS, oCNT, oA;
     const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
@@ -124,7 +124,7 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
     c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
     c.oRD = p; p += N;
-    c.oBS = p; p += N;
+    c.oBS = p; p += N; c.oPIV = p; p += (N + 1) / 2;
     c.oSTEP = p; p += (N + 1) / 2;
     c.lda = M.nSp + 1;                        // even for GRI (54): column accesses across rows are 2-way conflicted, rows are not
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
@@ -387,6 +387,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     double* A = WS(A);
     double* RD = WS(RD);
     int* STEP = reinterpret_cast<int*>(WS(STEP));
+    int* PIV = reinterpret_cast<int*>(WS(PIV));   // PIV[j] = row that became the pivot row of column j
     double* XCH = WS(XCH);
     double* row = A + t * lda;
     g.sync();
@@ -396,8 +397,16 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         for (int k = 0; k <= nSp; ++k) row[k] = 0.0;
         const double* JS = GS_JS;
         const int e1 = S.rowPtr[t + 1];
+        // JS and the column list stream from global memory (L2): four independent loads per round trip
+        int e = S.rowPtr[t];
 #pragma unroll 1
-        for (int e = S.rowPtr[t]; e < e1; ++e) row[S.entCol[e]] = -JS[e];
+        for (; e + 3 < e1; e += 4) {
+            const int c0 = S.entCol[e], c1 = S.entCol[e + 1], c2 = S.entCol[e + 2], c3 = S.entCol[e + 3];
+            const double v0 = JS[e], v1 = JS[e + 1], v2 = JS[e + 2], v3 = JS[e + 3];
+            row[c0] = -v0; row[c1] = -v1; row[c2] = -v2; row[c3] = -v3;
+        }
+#pragma unroll 1
+        for (; e < e1; ++e) row[S.entCol[e]] = -JS[e];
         row[nSp] = -WS(JT)[t];
         row[t] += dg;
         big = 0.0;
@@ -408,7 +417,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const double vv = 1.0 / big;
     bool done = (t >= nSp);
     int pos = t;
-    if (t >= nSp && t < N) { STEP[t] = t; RD[t] = 1.0 / dg; }
+    if (t >= nSp && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
 #pragma unroll 1
     for (int j = 0; j < nSp; ++j) {
         const double piv = done ? 0.0 : row[j];
@@ -440,7 +449,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const int ptid = reinterpret_cast<const int*>(sw + 1)[1];
         const double rd = sw[2];
         if (t == ptid) {
-            done = true; STEP[t] = j; RD[j] = rd;
+            done = true; STEP[t] = j; PIV[j] = t; RD[j] = rd;
             if (piv == 0.0) row[j] = LB_SMALL;
         } else if (!done) {
             if (pos == j) pos = ppos;
