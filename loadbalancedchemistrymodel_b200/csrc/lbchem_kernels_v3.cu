@@ -287,20 +287,14 @@ __device__ __forceinline__ double gather_species(const SMech& S, const double* o
     return (a0 + a1) + (a2 + a3);
 }
 
-// StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
-__device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
-    const Grp g(base);
+// tail of StandardChemistryModel::derivatives: dT/dt = -sum h_i w_i / (rho cp) from the species rates `d` (thread t owns
+// species t), CC and T current; writes dydt and counts one derivatives() evaluation
+__device__ __forceinline__ void finish_derivatives(const Grp& g, const Ctx* cx, double* base, double T, double d, double* dydt) {
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid;
-    g.sync();
-    const double T = y[nSp];
-    const double lnT = log(T), invT = 1.0 / T;
-    prepare(g, cx, base, y, T, lnT, true);
-    reaction_sweep(cx, base, 0, T, lnT, invT);
     const double RR = cx->O.RR;
     double rho = 0.0, cp = 0.0, dT = 0.0;
     if (t < nSp) {
-        const double d = gather_species(S, WS(OM), t);
         dydt[t] = d;
         const double ci = WS(CC)[t];
         const bool lo = T < S.Tc[t];
@@ -315,9 +309,22 @@ __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const doub
     g.sync();
 }
 
+// StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
+__device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, t = g.tid;
+    g.sync();
+    const double T = y[nSp];
+    const double lnT = log(T), invT = 1.0 / T;
+    prepare(g, cx, base, y, T, lnT, true);
+    reaction_sweep(cx, base, 0, T, lnT, invT);
+    finish_derivatives(g, cx, base, T, t < nSp ? gather_species(S, WS(OM), t) : 0.0, dydt);
+}
+
 // StandardChemistryModel::jacobian (A.9) into the sparse store: JS[entry] (species block, structural
 // non-zeros in (row, col) order), JT[i] = d(dc_i/dt)/dT by central difference; dfdx = species rates (A.4 quirk)
-__device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx) {
+__device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx, double* dydt0) {
     const Grp g(base);
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid, N = cx->nEqn;
@@ -332,7 +339,11 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
         prepare(g, cx, base, y, Tp, lnT, pass == 0);
         reaction_sweep(cx, base, pass == 0, Tp, lnT, invT);
         if (pass == 0) {
-            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? gather_species(S, WS(OM), t) : 0.0;
+            // species rates at (y, T): the dfdx slot (A.4 quirk) and, on request, the full derivatives() at the same state
+            // (adaptiveSolver's dydx0: the reference evaluates it separately from the same rates)
+            const double d0 = (t < nSp && (cx->O.dfdxIsDcdt || dydt0)) ? gather_species(S, WS(OM), t) : 0.0;
+            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? d0 : 0.0;
+            if (dydt0) finish_derivatives(g, cx, base, T, d0, dydt0);
             // gather program: acc += coef * k * c1 * c2 * c3, entry closed by the `last` flag
             const double* KFR = WS(A); const double* CC = WS(CC); double* JS = GS_JS;
             const int nR = S.nR;
@@ -511,7 +522,7 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
 // ------------------------------------------------------------------------------------------------
 // integrators (control flow identical to lbchem_kernels_v2.cu; only the heavy routines are calls)
 // ------------------------------------------------------------------------------------------------
-struct Cell { int fail; double theta; int kTarg; };
+struct Cell { int fail; double theta; int kTarg; int f0valid; };
 struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
 
 __constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
@@ -564,9 +575,8 @@ __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, doub
     const int t = g.tid, N = cx->nEqn;
     double dx = dxTry, err = 0.0;
     // dydx0 and the Jacobian are both evaluated at (y0, T0)
-    jacobian(cx, base, VEC(0), VEC(3));
+    jacobian(cx, base, VEC(0), VEC(3), VEC(2));
     if (t == 0) CNT(CNT_JAC)--;                 // counted per attempt in rosenbrock34_step
-    derivatives(cx, base, VEC(0), VEC(2));
     do {
         if (t == 0) CNT(CNT_ATTEMPTS)++;
         err = rosenbrock34_step(g, cx, base, cs, dx);
@@ -606,7 +616,15 @@ __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, 
         if (phase == 0) {
             if (it == 1) { if (t < N) yT[t] = y0[t] + dy[t]; }
             else if (it > 1) { if (t < N) yT[t] += dy[t]; }
-            derivatives(cx, base, it == 0 ? y0 : yT, f);
+            if (it == 0 && cs.f0valid) {
+                // f(y0) is the same for every column and every retry of this step: the reference re-evaluates it,
+                // we keep it in V3 (counted as an evaluation all the same)
+                if (t < N) f[t] = VEC(3)[t];
+                if (t == 0) CNT(CNT_RHS)++;
+            } else {
+                derivatives(cx, base, it == 0 ? y0 : yT, f);
+                if (it == 0) { if (t < N) VEC(3)[t] = f[t]; cs.f0valid = 1; }
+            }
             if (it == 1 && k <= 1) phase = 1;
         }
         double* rhs;
@@ -664,6 +682,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
     double dx = step.dxTry;
     g.sync();
     if (t < N) { y0[t] = y[t]; scale[t] = absTol + relTol * fabs(y[t]); }
+    cs.f0valid = 0;
     dxOpt[0] = fabs(0.1 * dx);
     if (step.first || step.prevReject) cs.theta = 2.0 * jacRedo;
     if (step.first) {
@@ -674,7 +693,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
         cs.kTarg = kt;
     }
     bool jacUpdated = false;
-    if (cs.theta > jacRedo) { jacobian(cx, base, y, VEC(3)); jacUpdated = true; }
+    if (cs.theta > jacRedo) { jacobian(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
     int k = 0;
     double dxNew = fabs(dx);
     bool firstk = true;
@@ -756,7 +775,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
             step.prevReject = 1;
             if (!jacUpdated) {
                 cs.theta = 2.0 * jacRedo;
-                if (cs.theta > jacRedo && !jacUpdated) { jacobian(cx, base, y, VEC(3)); jacUpdated = true; }
+                if (cs.theta > jacRedo && !jacUpdated) { jacobian(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
             }
         }
     }
@@ -867,7 +886,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
         double dtChem = B.deltaTChem[cell];
         if (t < CNT_N) CNT(t) = 0;
-        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1;
+        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0;
         int status;
         double Tend = T0;
         double* y = VEC(0);
