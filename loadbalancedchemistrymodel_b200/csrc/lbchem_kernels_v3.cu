@@ -693,7 +693,13 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
         cs.kTarg = kt;
     }
     bool jacUpdated = false;
-    if (cs.theta > jacRedo) { jacobian(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
+    if (cs.theta > jacRedo) {
+        // the Jacobian's first rate sweep is at (y0, T0): it also yields f(y0) for the first Euler sub-step of every column
+        jacobian(cx, base, y, VEC(8), VEC(3));
+        if (t == 0) CNT(CNT_RHS)--;            // counted when seul() consumes it
+        cs.f0valid = 1;
+        jacUpdated = true;
+    }
     int k = 0;
     double dxNew = fabs(dx);
     bool firstk = true;
