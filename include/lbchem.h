@@ -146,6 +146,22 @@ int lbchem_get_options(lbchem_handle h, lbchem_options* opts);
 const char* lbchem_last_error(lbchem_handle h);
 
 /*
+ * Mechanism reduction of the LoadBalancedTDAC model: `reduction{active on; method DAC; tolerance; initialSet{...}}`
+ * (reference tests/Cases/Case-chemistry/constant/chemistryProperties:35-66; automaticSIS off). When active, every cell
+ * of the batches that follow is reduced before it is integrated, as solveCell does with mechRed()->active()
+ * (reference src/chemistryModel/LoadBalancedTDACChemistryModel/LoadBalancedTDACChemistryModel.C:385-393,399-415):
+ * species are kept by a breadth-first search over the direct-interaction coefficients from the initial set,
+ * reactions touching a removed species are switched off, only the kept species (+T, p) are integrated, third-body
+ * sums, rho and cp still use every species. Tout returns the temperature the cell came in with (the reference's
+ * reduced call aliases T and p, :406-409). Solvers: seulex, Rosenbrock34. tabulation{} (ISAT) is host-side and not
+ * part of this library.
+ *   init_species [n_init]  indices of the initialSet species (1..8 entries), in dictionary order
+ */
+int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int32_t n_init, const int32_t* init_species);
+/* NsDAC_ of the first n cells of the last batch (HOST pointer); valid after a solve with reduction active. */
+int lbchem_get_active_species(lbchem_handle h, int64_t n, int32_t* n_active);
+
+/*
  * Integrate n cells over their flow time step. DEVICE pointers, stream-ordered on `stream`
  * (a cudaStream_t passed as void*; NULL = legacy default stream).
  *   Y        [nSp][ldy]  mass fractions, field-major (species i, cell c at Y[i*ldy + c]), in

@@ -138,6 +138,8 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_solve_batch.argtypes = sig + [C.c_void_p]
     lib.lbchem_solve_batch_host.argtypes = sig
     lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
+    lib.lbchem_set_reduction.argtypes = [H, C.c_int32, C.c_double, C.c_int32, _ip]
+    lib.lbchem_get_active_species.argtypes = [H, C.c_int64, _ip]
     lib.lbchem_probe.argtypes = [H, C.c_int32, C.c_int32, _dp, C.c_int32, _dp, C.c_int32]
     lib.lbchem_fp64_peak.argtypes = [C.c_int, C.c_double, _dp, _dp]
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
@@ -151,7 +153,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak"
+    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species"
 ).split()
 
 
@@ -221,6 +223,21 @@ class Chemistry:
     def set_options(self, options: Options):
         self._check(self.lib.lbchem_set_options(self.h, C.byref(options)), "lbchem_set_options")
         self.options = options
+
+    def set_reduction(self, tolerance=None, initial_set=None):
+        """``reduction{active on; method DAC; tolerance; initialSet}`` of LoadBalancedTDAC; ``tolerance=None`` switches it off."""
+        if tolerance is None:
+            self._check(self.lib.lbchem_set_reduction(self.h, 0, 0.0, 0, None), "lbchem_set_reduction")
+            return
+        init = np.ascontiguousarray(initial_set, dtype=np.int32)
+        self._check(self.lib.lbchem_set_reduction(self.h, 1, float(tolerance), int(init.size), _as_ip(init)),
+                    "lbchem_set_reduction")
+
+    def active_species(self, n: int) -> np.ndarray:
+        """NsDAC_ of the first n cells of the last reduced batch."""
+        out = np.zeros(int(n), np.int32)
+        self._check(self.lib.lbchem_get_active_species(self.h, int(n), _as_ip(out)), "lbchem_get_active_species")
+        return out
 
     def stats(self) -> dict:
         st = Stats()

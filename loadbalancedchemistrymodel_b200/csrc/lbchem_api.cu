@@ -16,6 +16,7 @@
 
 int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err);
 int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
+int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut);
 bool lb_v2_supported_size(int nEqn);
 cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
 int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
@@ -74,6 +75,9 @@ struct lbchem_handle_t {
     bool v2Built = false, useV2 = false, useV3 = false;
     int v3Groups = 0, v3Ws = 0; size_t v3Smem = 0;
     double* dScratch = nullptr; int scratchStride = 0; size_t scratchCap = 0;
+    // DAC reduction (LoadBalancedTDAC): host copy of the program, device copy, per-cell NsDAC_ of the last batch
+    std::vector<int> dacProg; int dacPairs = 0; int* dDac = nullptr; bool dacOn = false;
+    int* dNActive = nullptr; long long nActiveCap = 0, nActiveOff = 0;
     int v2Groups = 0; size_t v2Smem = 0;
     double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
     void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
@@ -388,6 +392,10 @@ int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) 
     if (rc != LBCHEM_OK) return rc;
     {
         std::string e;
+        {
+            const int32_t seed = 0;
+            if (lb_dac_program(mech, 1e-4, 1, &seed, h->dacProg, &h->dacPairs) != 0) h->dacProg.clear();
+        }
         const int r2 = lb_v2_build(mech, &h->V2, h->allocs, e);
         if (r2 < 0) return fail(h, r2, e);
         h->v2Built = (r2 == 0);
@@ -409,6 +417,8 @@ int lbchem_destroy(lbchem_handle h) {
     if (h->dQueue) cudaFree(h->dQueue);
     if (h->dStats) cudaFree(h->dStats);
     if (h->dScratch) cudaFree(h->dScratch);
+    if (h->dDac) cudaFree(h->dDac);
+    if (h->dNActive) cudaFree(h->dNActive);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     for (Slot& s : h->slots) {
@@ -441,6 +451,52 @@ int lbchem_get_options(lbchem_handle h, lbchem_options* o) {
 
 const char* lbchem_last_error(lbchem_handle h) { return h ? h->err.c_str() : "null handle"; }
 
+int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int32_t n_init, const int32_t* init_species) {
+    if (!h) return LBCHEM_E_INVALID;
+    CK(cudaSetDevice(h->device));
+    if (!active) { h->dacOn = false; h->V2.dac = nullptr; return LBCHEM_OK; }
+    if (h->dacProg.empty() || !h->v2Built)
+        return fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction needs the packed mechanism of the compact-code kernel (nSp <= 62, integer stoichiometry)");
+    if (!(tolerance > 0.0) || n_init < 1 || n_init > 8 || !init_species)
+        return fail(h, LBCHEM_E_INVALID, "reduction: tolerance must be > 0 and the initial set must hold 1..8 species");
+    for (int i = 0; i < n_init; ++i)
+        if (init_species[i] < 0 || init_species[i] >= h->M.nSp) return fail(h, LBCHEM_E_INVALID, "reduction: initial-set species out of range");
+    {
+        V2Mech probe = h->V2;
+        lb_v3_workspace(probe, LBCHEM_SOLVER_ROSENBROCK34, 1e-2, 1e-12);
+        const int cap = std::max(h->V2.nSp * (h->V2.nSp + 1), 2 * h->V2.nR);
+        if (h->dacPairs > cap) return fail(h, LBCHEM_E_UNSUPPORTED, "reduction: species-pair table does not fit the per-cell workspace");
+    }
+    h->dacProg[7] = n_init;
+    for (int i = 0; i < 8; ++i) h->dacProg[8 + i] = i < n_init ? init_species[i] : 0;
+    memcpy(&h->dacProg[16], &tolerance, 8);
+    if (!h->dDac) CK(cudaMalloc(&h->dDac, h->dacProg.size() * sizeof(int)));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(h->dDac, h->dacProg.data(), h->dacProg.size() * sizeof(int), cudaMemcpyHostToDevice));
+    h->V2.dac = h->dDac;
+    h->dacOn = true;
+    return LBCHEM_OK;
+}
+
+int lbchem_get_active_species(lbchem_handle h, int64_t n, int32_t* n_active) {
+    if (!h || !n_active || n < 0) return LBCHEM_E_INVALID;
+    CK(cudaSetDevice(h->device));
+    if (!h->dacOn || !h->dNActive || n > h->lastN || n > h->nActiveCap)
+        return fail(h, LBCHEM_E_INVALID, "no reduced batch of that size has been solved");
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(n_active, h->dNActive, (size_t)n * sizeof(int), cudaMemcpyDeviceToHost));
+    return LBCHEM_OK;
+}
+
+static int reserve_nactive(lbchem_handle h, long long n) {
+    if (!h->dacOn || n <= h->nActiveCap) return LBCHEM_OK;
+    if (h->dNActive) cudaFree(h->dNActive);
+    h->dNActive = nullptr; h->nActiveCap = 0;
+    CK(cudaMalloc(&h->dNActive, (size_t)n * sizeof(int)));
+    h->nActiveCap = n;
+    return LBCHEM_OK;
+}
+
 static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, const double* T, const double* p,
                   const double* rho, const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR,
                   double* Tout, double* cost, int32_t* status, unsigned long long* queue, cudaStream_t s) {
@@ -448,7 +504,13 @@ static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, 
     B.n = n; B.ldy = ldy; B.Y = Y; B.T = T; B.p = p; B.rho = rho; B.deltaT = deltaT; B.deltaTUniform = deltaT_uniform;
     B.deltaTChem = deltaTChem; B.RR = RR; B.Tout = Tout; B.cost = cost; B.status = status; B.order = nullptr;
     B.queue = queue; B.stats = h->dStats; B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
+    B.nActive = nullptr;
     CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
+    if (h->dacOn) {
+        if (!h->useV3)
+            return fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction runs in the compact-code kernel only (solver seulex or Rosenbrock34, nEqn <= 64)");
+        if (h->dNActive && h->nActiveOff + n <= h->nActiveCap) B.nActive = h->dNActive + h->nActiveOff;
+    }
     if (h->useV3) {
         long long grid3 = h->nSM;
         const long long need3 = (n + h->v3Groups - 1) / h->v3Groups;
@@ -485,6 +547,8 @@ int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy, const double* Y,
     CK(cudaSetDevice(h->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     h->launches = 0; h->hostPath = false; h->lastN = n;
+    { int rc = reserve_nactive(h, n); if (rc != LBCHEM_OK) return rc; }
+    h->nActiveOff = 0;
     CK(cudaMemsetAsync(h->dStats, 0, 8 * sizeof(unsigned long long), s));
     CK(cudaEventRecord(h->ev0, s));
     if (n > 0) {
@@ -529,6 +593,7 @@ int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy, const doubl
     if (const char* e = getenv("LBCHEM_CHUNK")) if (atoll(e) > 0) chunk = atoll(e);
     if (chunk > n) chunk = n > 0 ? n : 1;
     h->launches = 0; h->hostPath = true; h->lastN = n; h->evValid = false;
+    { int rc = reserve_nactive(h, n); if (rc != LBCHEM_OK) return rc; }
     for (Slot& s : h->slots) s.used = false;
     CK(cudaMemset(h->dStats, 0, 8 * sizeof(unsigned long long)));
     int k = 0;
@@ -546,6 +611,7 @@ int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy, const doubl
         if (deltaT) CK(cudaMemcpyAsync(s.dT, deltaT + c0, w, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(s.dtc, deltaTChem + c0, w, cudaMemcpyHostToDevice, st));
         if (!s.used) CK(cudaEventRecord(s.k0, st));
+        h->nActiveOff = c0;
         rc = launch(h, m, s.cap, s.Y, s.T, s.p, s.rho, deltaT ? s.dT : nullptr, deltaT_uniform, s.dtc, s.RR, s.Tout, s.cost,
                     s.status, s.queue, st);
         if (rc != LBCHEM_OK) return rc;

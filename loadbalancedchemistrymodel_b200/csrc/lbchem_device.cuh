@@ -70,6 +70,7 @@ struct BatchArgs {
     unsigned long long* stats;   // 8 counters: steps, attempts, jac, lu, solve, rhs, failed, cells
     double* scratch;             // v3 kernel: per-group global scratch (sparse Jacobian + seulex table), L2-resident
     int scratchStride;           // doubles per group
+    int* nActive;                // optional: number of active species DAC kept for each cell (NsDAC_)
 };
 
 // probe kinds (test hooks that run the same device functions as the integrator)

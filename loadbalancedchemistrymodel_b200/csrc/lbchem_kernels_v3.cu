@@ -110,8 +110,9 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oPIV, oXCH, oXS, oCNT, oA;
+    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oPIV, oXCH, oXS, oCNT, oA, oMSK;
     const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
+    const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
 enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N };
@@ -120,6 +121,7 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
     int p = 32;                               // reduction scratch
     c.oXCH = p; p += 16; c.oXS = p; p += 2; c.oCNT = p; p += 4;
+    c.oMSK = p; p += (M.nR + 63) / 64 + 1;    // DAC: disabled-reaction bits (by packed position), then the active-species word
     c.oV = p; p += 9 * N;
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
     c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
@@ -191,11 +193,15 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
     const int nR = S.nR, nFall = cx->nFall;
     double* OM = WS(OM);
     const double *GL = WS(GL), *GH = WS(GH), *ME = WS(ME), *CC = WS(CC);
+    // DAC: reactions touching a removed species are skipped (TDACChemistryModel::omega, reactionsDisabled_)
+    const unsigned long long* MSK = reinterpret_cast<const unsigned long long*>(WS(MSK));
+    const bool dac = cx->dac != nullptr;
+#define RX_OFF(p) (dac && ((MSK[(p) >> 6] >> ((p) & 63)) & 1ull))
     // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
 #pragma unroll 1
     for (int p = g.tid; p < nR; p += TPC) {
         double val = 1.0;
-        if (V2_HASEXP(S.info[p])) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
+        if (V2_HASEXP(S.info[p]) && !RX_OFF(p)) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
         OM[p] = val;
     }
     g.sync();
@@ -204,6 +210,7 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
 #pragma unroll 1
         for (int q = g.tid; q < nFall; q += TPC) {
             const int p = nR - nFall + q;
+            if (RX_OFF(p)) continue;
             const unsigned iw = S.info[p];
             const double* f = S.fall + 8 * V2_FALL(iw);
             double k0 = f[0];
@@ -230,6 +237,7 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
     double* KF = WS(A); double* KR = KF + nR;
 #pragma unroll 1
     for (int p = g.tid; p < nR; p += TPC) {
+        if (RX_OFF(p)) { OM[p] = 0.0; if (keep) { KF[p] = 0.0; KR[p] = 0.0; } continue; }
         const unsigned iw = S.info[p];
         const unsigned ty = V2_RTYPE(iw);
         double k = OM[p];
@@ -261,6 +269,7 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
         OM[p] = f - b;
         if (keep) { KF[p] = k; KR[p] = kr; }
     }
+#undef RX_OFF
     g.sync();
 }
 
@@ -426,11 +435,15 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     }
     if (g.any(t < N && big == 0.0, 2)) return LBCHEM_CELL_SINGULAR;
     const double vv = 1.0 / big;
-    bool done = (t >= nSp);
+    // DAC: the rows and columns of removed species hold only the diagonal dg (no reaction touches them), i.e. the reduced
+    // system of the reference embedded in the full index space: such a row is its own pivot row and its column is skipped
+    const unsigned long long act = cx->dac ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(S.nR + 63) >> 6] : ~0ull;
+    bool done = (t >= nSp) || !((act >> t) & 1ull);
     int pos = t;
-    if (t >= nSp && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
+    if (done && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
 #pragma unroll 1
     for (int j = 0; j < nSp; ++j) {
+        if (!((act >> j) & 1ull)) continue;
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
         const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
@@ -496,10 +509,13 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     g.sync();
     const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
     double bt = t < N ? x[t] : 0.0;
-    const bool sp = t < nSp;
+    const unsigned long long act = cx->dac ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(cx->S.nR + 63) >> 6] : ~0ull;
+    const bool sp = t < nSp && ((act >> t) & 1ull);
+    if (t < nSp && !sp) x[t] = bt * RD[t];          // removed species: decoupled diagonal row
     // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
     for (int j = 0; j < nSp; ++j) {
+        if (!((act >> j) & 1ull)) continue;
         if (step == j) BS[j] = bt;
         g.sync();
         if (sp && step > j) bt = fma(-row[j], BS[j], bt);
@@ -511,6 +527,7 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     if (sp) bt = fma(-row[nSp], BS[nSp], bt);
 #pragma unroll 1
     for (int j = nSp - 1; j >= 0; --j) {
+        if (!((act >> j) & 1ull)) continue;
         if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
         g.sync();
         if (sp && step < j) bt = fma(-row[j], BS[j], bt);
@@ -519,10 +536,126 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     g.sync();
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// DAC::reduceMechanism (automaticSIS off) for the cell whose state is y: fills the disabled-reaction bits and the
+// active-species word of MSK and returns NsDAC_. Rates of ALL reactions at (c, T) -> per species A the numerators of
+// r_AB (signed sums in reaction order), P_A, C_A -> breadth-first search from the initial set by warp 0 (a species is
+// queued once, in the reference's order: neighbours in first-appearance order) with R_B = max(R_B, R_u r_uB).
+// Uses the matrix region for the numerators and V1..V4 as scratch: call before the integration starts.
+// ------------------------------------------------------------------------------------------------
+__device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double* y) {
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, nR = S.nR, t = g.tid;
+    const int* D = cx->dac;
+    unsigned long long* MSK = reinterpret_cast<unsigned long long*>(WS(MSK));
+    const int nW = (nR + 63) >> 6;
+    g.sync();
+    if (t <= nW) MSK[t] = 0ull;                       // every reaction takes part in the rate evaluation
+    const double T = y[nSp];
+    const double lnT = log(T), invT = 1.0 / T;
+    prepare(g, cx, base, y, T, lnT, true);
+    reaction_sweep(cx, base, 0, T, lnT, invT);
+    const double* OM = WS(OM);
+    double* NUM = WS(A);
+    double *PA = VEC(1), *CA = VEC(2), *RV = VEC(3);
+    const int* pairPtr = D + D[1];
+    if (t < nSp) {
+        const int* termPtr = D + D[2]; const unsigned* term = reinterpret_cast<const unsigned*>(D + D[3]);
+        const int* pcPtr = D + D[4]; const unsigned* pc = reinterpret_cast<const unsigned*>(D + D[5]);
+        int e = pairPtr[t];
+        double acc = 0.0;
+        const int k1 = termPtr[t + 1];
+#pragma unroll 1
+        for (int k = termPtr[t]; k < k1; ++k) {
+            const unsigned w = term[k];
+            acc = __dadd_rn(acc, __dmul_rn((double)(int)(signed char)(w >> 16), OM[w & 0xffffu]));
+            if ((w >> 24) & 1u) { NUM[e++] = acc; acc = 0.0; }
+        }
+        double pa = 0.0, ca = 0.0;
+        const int q1 = pcPtr[t + 1];
+#pragma unroll 1
+        for (int k = pcPtr[t]; k < q1; ++k) {
+            const unsigned w = pc[k];
+            const double wA = __dmul_rn((double)(int)(signed char)(w >> 16), OM[w & 0xffffu]);
+            if (wA > 0.0) pa += wA; else ca += -wA;
+        }
+        PA[t] = pa; CA[t] = ca; RV[t] = 0.0;
+    }
+    g.sync();
+    if (g.warp == 0) {
+        unsigned char* Q = reinterpret_cast<unsigned char*>(VEC(4));
+        const unsigned char* nb = reinterpret_cast<const unsigned char*>(D + D[6]);
+        const double tol = __hiloint2double(D[17], D[16]);
+        unsigned long long act = 0ull;
+        int head = 0, tail = 0;
+        const int nInit = D[7];
+        for (int i = 0; i < nInit; ++i) {
+            const int q = D[8 + i];
+            if (!((act >> q) & 1ull)) {
+                act |= 1ull << q;
+                if (g.lane == 0) { Q[tail] = (unsigned char)q; RV[q] = 1.0; }
+                ++tail;
+            }
+        }
+        __syncwarp();
+#pragma unroll 1
+        while (head < tail) {
+            const int u = Q[head++];
+            const double Den = fmax(PA[u], CA[u]);
+            if (Den > LB_VSMALL) {
+                const int e0 = pairPtr[u], n = pairPtr[u + 1] - e0;
+                const double Ru = RV[u];
+#pragma unroll 1
+                for (int v0 = 0; v0 < n; v0 += 32) {
+                    const int v = v0 + g.lane;
+                    bool cond = false; int Bsp = 0; double Rt = 0.0;
+                    if (v < n) {
+                        Bsp = nb[e0 + v];
+                        double r = fabs(NUM[e0 + v]) / Den;
+                        if (r > 1.0) r = 1.0;
+                        Rt = Ru * r;
+                        cond = Rt >= tol;
+                    }
+                    if (cond && Rt > RV[Bsp]) RV[Bsp] = Rt;
+                    const bool nw = cond && !((act >> Bsp) & 1ull);
+                    const unsigned m = __ballot_sync(0xffffffffu, nw);
+                    if (nw) Q[tail + __popc(m & ((1u << g.lane) - 1u))] = (unsigned char)Bsp;
+                    tail += __popc(m);
+                    const unsigned lo = __reduce_or_sync(0xffffffffu, (nw && Bsp < 32) ? 1u << Bsp : 0u);
+                    const unsigned hi = __reduce_or_sync(0xffffffffu, (nw && Bsp >= 32) ? 1u << (Bsp - 32) : 0u);
+                    act |= ((unsigned long long)hi << 32) | lo;
+                    __syncwarp();
+                }
+            }
+        }
+        if (g.lane == 0) MSK[nW] = act;
+    }
+    g.sync();
+    const unsigned long long act = MSK[nW];
+    g.sync();
+#pragma unroll 1
+    for (int c = 0; c < nW; ++c) {
+        const int p = c * 64 + t;
+        bool dis = false;
+        if (p < nR) {
+            const unsigned iw = S.info[p];
+            const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
+            for (unsigned s = 0; s < V2_NL(iw); ++s) dis = dis || !((act >> V2_SP(V2_SLOT(lp, s))) & 1ull);
+            for (unsigned s = 0; s < V2_NR(iw); ++s) dis = dis || !((act >> V2_SP(V2_SLOT(rp, s))) & 1ull);
+        }
+        const unsigned b = __ballot_sync(0xffffffffu, dis);
+        if (g.lane == 0) reinterpret_cast<unsigned*>(MSK)[2 * c + g.warp] = b;
+    }
+    g.sync();
+    return __popcll(act);
+}
+
 // ------------------------------------------------------------------------------------------------
 // integrators (control flow identical to lbchem_kernels_v2.cu; only the heavy routines are calls)
 // ------------------------------------------------------------------------------------------------
-struct Cell { int fail; double theta; int kTarg; int f0valid; };
+struct Cell { int fail; double theta; int kTarg; int f0valid; int nOde; };   // nOde: equations of the ODE system (NsDAC_+2 when reduced)
 struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
 
 __constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
@@ -733,7 +866,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
                 }
             }
             if (k != 0) {
-                const double err = sqrt(g.sum(s, 1) / N);
+                const double err = sqrt(g.sum(s, 1) / cs.nOde);
                 if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
                 if (err > 1 / LB_SMALL || (k > 1 && err >= errOld)) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
                 errOld = fmin(4 * err, 1.0);
@@ -868,7 +1001,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         cxw->O = O; cxw->O.solver = SOLVER;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
-        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN;
+        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = M.dac;
         cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
     }
     __syncthreads();
@@ -892,7 +1025,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
         double dtChem = B.deltaTChem[cell];
         if (t < CNT_N) CNT(t) = 0;
-        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0;
+        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0; cs.nOde = cx->nEqn;
         int status;
         double Tend = T0;
         double* y = VEC(0);
@@ -901,6 +1034,12 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
             if (t == nSp) y[nSp] = T0;
             if (t == nSp + 1) y[nSp + 1] = p0;
             g.sync();
+            if (cx->dac) {
+                // LoadBalancedTDAC solveCell with mechRed()->active() (reference LoadBalancedTDACChemistryModel.C:385-393)
+                const int ns = dac_reduce(cx, base, y);
+                if (t == 0 && B.nActive) B.nActive[cell] = ns;
+                cs.nOde = ns + 2;
+            }
             double timeLeft = deltaT;
             while (timeLeft > LB_SMALL) {
                 double dt = timeLeft;
@@ -916,7 +1055,9 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
                 const double c0 = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t];
                 B.RR[(size_t)t * B.ldy + cell] = (y[t] - c0) * S.W[t] / deltaT;
             }
-            Tend = y[nSp];
+            // the reduced call of the reference passes cData.T() for both T and p (:406-409): the aliased reference ends up
+            // holding the p slot, i.e. the temperature the cell came in with
+            Tend = cx->dac ? T0 : y[nSp];
             status = cs.fail ? cs.fail : LBCHEM_CELL_OK;
         } else {
             if (t < nSp) B.RR[(size_t)t * B.ldy + cell] = 0.0;

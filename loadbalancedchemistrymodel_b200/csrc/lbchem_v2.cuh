@@ -45,6 +45,7 @@ struct V2Mech {
     int jMaxTerms;
     // the same program dealt to 128 threads (v3 kernel)
     const unsigned long long* jterm3; const int* jthrEnt3; const int* jthrN3;
+    const int* dac;                      // DAC program (lb_dac_program) when reduction is active, else null (v3 kernel)
     int tbRows;                          // rows of the seulex extrapolation table held per cell
     int wsDoubles;                       // per-cell workspace in doubles
 };

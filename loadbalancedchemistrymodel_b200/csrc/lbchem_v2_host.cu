@@ -37,15 +37,11 @@ bool small_int(double x, int lo, int hi) { return x == std::floor(x) && x >= lo 
 }  // namespace
 
 // returns 0 = built, 1 = mechanism outside the fast path's class (caller keeps the general kernel), <0 = error
-int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err) {
-    const int nSp = m->n_species, nR = m->n_reactions, nEff = m->n_eff;
-    const int N = nSp + 2;
-    if (N > 64 || nSp > 254 || nR > 32000 || nEff > 31 || nR < 1) return 1;
-    V2Mech M{};
-    M.nSp = nSp; M.nR = nR; M.nEqn = N; M.nEff = nEff;
 
-    // ---- reaction order: homogeneous rounds of 64 (exp / no exp / irreversible / third body / fall-off)
-    std::vector<int> order(nR), posOf(nR);
+// position of each reaction in the packed tables: classes exp / no exp / irreversible / third body / fall-off
+static void reaction_order(const lbchem_mech_desc* m, std::vector<int>& order, std::vector<int>& posOf) {
+    const int nR = m->n_reactions;
+    order.resize(nR); posOf.resize(nR);
     auto cls = [&](int r) {
         if (m->rtype[r] >= LBCHEM_R_FALLOFF_LINDEMANN) return 4;
         if (m->rtype[r] == LBCHEM_R_THIRD_BODY) return 3;
@@ -56,6 +52,93 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     for (int r = 0; r < nR; ++r) order[r] = r;
     std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return cls(a) < cls(b); });
     for (int p = 0; p < nR; ++p) posOf[order[p]] = p;
+}
+
+// DAC program (chemistryReductionMethods::DAC::reduceMechanism; reference call site LoadBalancedTDACChemistryModel.C:388).
+// One int array, offsets in ints from its start:
+//   [0] nPairs  [1] pairPtr  [2] termPtr  [3] term  [4] pcPtr  [5] pc  [6] nb (bytes)  [7] nInit  [8..15] initial set
+//   [16],[17] tolerance (lo, hi words)
+// pairPtr[A]..pairPtr[A+1]: the (A,B) pairs of species A in first-appearance order of B (the rABPos order);
+// term: per species the contributions net_nu_A(reaction) * omega[pos] to its pair numerators, pair by pair, reactions
+// ascending (bit 24 closes a pair); pc: per species the net_nu_A * omega[pos] of every reaction holding A (P_A / C_A).
+int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut) {
+    const int nSp = m->n_species, nR = m->n_reactions;
+    if (nSp > 64 || nInit < 1 || nInit > 8 || !(tol > 0.0)) return 1;
+    std::vector<int> order, posOf;
+    reaction_order(m, order, posOf);
+    struct Contribution { int pos, coef; };
+    std::vector<std::vector<int>> nbOf(nSp);                                   // B list per A
+    std::vector<std::map<int, std::vector<Contribution>>> termsOf(nSp);        // per A: B -> contributions
+    std::vector<std::vector<Contribution>> pcOf(nSp);
+    for (int r = 0; r < nR; ++r) {
+        std::vector<int> ids, net;                                             // species of the reaction, lhs then rhs, each once
+        auto add = [&](int s, int nu) {
+            for (size_t q = 0; q < ids.size(); ++q) if (ids[q] == s) { net[q] += nu; return; }
+            ids.push_back(s); net.push_back(nu);
+        };
+        for (int k = m->lhs_ptr[r]; k < m->lhs_ptr[r + 1]; ++k) {
+            if (m->lhs_nu[k] != std::floor(m->lhs_nu[k]) || m->lhs_nu[k] > 100) return 1;
+            add(m->lhs_species[k], -(int)m->lhs_nu[k]);
+        }
+        for (int k = m->rhs_ptr[r]; k < m->rhs_ptr[r + 1]; ++k) {
+            if (m->rhs_nu[k] != std::floor(m->rhs_nu[k]) || m->rhs_nu[k] > 100) return 1;
+            add(m->rhs_species[k], (int)m->rhs_nu[k]);
+        }
+        for (size_t a = 0; a < ids.size(); ++a) {
+            const int A = ids[a];
+            if (net[a] < -127 || net[a] > 127) return 1;
+            for (size_t b = 0; b < ids.size(); ++b) {
+                if (b == a) continue;
+                const int Bsp = ids[b];
+                if (!termsOf[A].count(Bsp)) nbOf[A].push_back(Bsp);
+                termsOf[A][Bsp].push_back({posOf[r], net[a]});
+            }
+            pcOf[A].push_back({posOf[r], net[a]});
+        }
+    }
+    std::vector<int> pairPtr(nSp + 1, 0), termPtr(nSp + 1, 0), pcPtr(nSp + 1, 0);
+    std::vector<unsigned> term, pc; std::vector<unsigned char> nb;
+    for (int A = 0; A < nSp; ++A) {
+        for (int Bsp : nbOf[A]) {
+            const auto& L = termsOf[A][Bsp];
+            for (size_t q = 0; q < L.size(); ++q)
+                term.push_back((unsigned)L[q].pos | ((unsigned)(uint8_t)(int8_t)L[q].coef << 16) | ((q + 1 == L.size()) ? 1u << 24 : 0u));
+            nb.push_back((unsigned char)Bsp);
+        }
+        for (const auto& c : pcOf[A]) pc.push_back((unsigned)c.pos | ((unsigned)(uint8_t)(int8_t)c.coef << 16));
+        pairPtr[A + 1] = (int)nb.size(); termPtr[A + 1] = (int)term.size(); pcPtr[A + 1] = (int)pc.size();
+    }
+    while (nb.size() % 4) nb.push_back(0);
+    prog.assign(18, 0);
+    prog[0] = pairPtr[nSp];
+    auto put = [&](int slot, const void* src, size_t bytes) {
+        prog[slot] = (int)prog.size();
+        const int* s = static_cast<const int*>(src);
+        prog.insert(prog.end(), s, s + bytes / 4);
+    };
+    put(1, pairPtr.data(), pairPtr.size() * 4); put(2, termPtr.data(), termPtr.size() * 4);
+    if (term.empty()) term.push_back(0);
+    if (pc.empty()) pc.push_back(0);
+    if (nb.empty()) nb.resize(4, 0);
+    put(3, term.data(), term.size() * 4); put(4, pcPtr.data(), pcPtr.size() * 4); put(5, pc.data(), pc.size() * 4);
+    put(6, nb.data(), nb.size());
+    prog[7] = nInit;
+    for (int i = 0; i < nInit; ++i) { if (init[i] < 0 || init[i] >= nSp) return 1; prog[8 + i] = init[i]; }
+    std::memcpy(&prog[16], &tol, 8);
+    if (nPairsOut) *nPairsOut = pairPtr[nSp];
+    return 0;
+}
+
+int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err) {
+    const int nSp = m->n_species, nR = m->n_reactions, nEff = m->n_eff;
+    const int N = nSp + 2;
+    if (N > 64 || nSp > 254 || nR > 32000 || nEff > 31 || nR < 1) return 1;
+    V2Mech M{};
+    M.nSp = nSp; M.nR = nR; M.nEqn = N; M.nEff = nEff;
+
+    // ---- reaction order: homogeneous rounds of 64 (exp / no exp / irreversible / third body / fall-off)
+    std::vector<int> order, posOf;
+    reaction_order(m, order, posOf);
 
     std::vector<double> tcTab;
     std::vector<double> A(nR), beta(nR), Ta(nR), fall;

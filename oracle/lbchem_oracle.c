@@ -53,6 +53,8 @@ typedef struct oracle_mech {
 typedef struct {
     lbchem_options o;
     int seulex_errold_max;  /* 0: errOld=min(4err,1) (OpenFOAM text as recalled); 1: NR3 max(4err,1) */
+    /* reduction{} dictionary of LoadBalancedTDAC (reference tests/Cases/Case-chemistry/constant/chemistryProperties:35-66) */
+    int dac_active; double dac_tol; int dac_ninit; int dac_init[64];
 } oracle_opts;
 
 static void* dup_mem(const void* p, size_t bytes) {
@@ -151,6 +153,14 @@ typedef struct {
     double *RRm, *src;
     ocounters cnt;
     int fail;              /* LBCHEM_CELL_* of the current cell */
+    /* TDACChemistryModel members used while a DAC-reduced mechanism is being integrated */
+    int red;               /* 1 while nSpecie_ == NsDAC_ (between reduceMechanism and the reset at TDAC solveCell :431-434) */
+    int NsDAC;
+    int *s2c, *c2s;        /* simplifiedToCompleteIndex_, completeToSimplifiedIndex_ */
+    unsigned char* rdis;   /* reactionsDisabled_ */
+    double *completeC, *simplC;
+    /* DAC::reduceMechanism scratch */
+    double *rABNum, *PA, *CA, *Rvalue; int *rABPos, *rABOther, *NbInit, *queue; unsigned char* act;
 } ows;
 
 static ows* ows_create(const oracle_mech* M, const oracle_opts* O) {
@@ -165,6 +175,17 @@ static ows* ows_create(const oracle_mech* M, const oracle_opts* O) {
     w->RRm = (double*)calloc((size_t)n * n, 8);
     w->table = (double*)calloc((size_t)12 * n, 8);
     w->piv = (int*)calloc(n, sizeof(int));
+    {
+        const int nSp = M->nSp, nR = M->nR;
+        w->s2c = (int*)calloc(nSp, sizeof(int)); w->c2s = (int*)calloc(nSp, sizeof(int));
+        w->rdis = (unsigned char*)calloc(nR ? nR : 1, 1);
+        w->completeC = (double*)calloc(nSp, 8); w->simplC = (double*)calloc(n, 8);
+        w->rABNum = (double*)calloc((size_t)nSp * nSp, 8);
+        w->PA = (double*)calloc(nSp, 8); w->CA = (double*)calloc(nSp, 8); w->Rvalue = (double*)calloc(nSp, 8);
+        w->rABPos = (int*)calloc((size_t)nSp * nSp, sizeof(int)); w->rABOther = (int*)calloc((size_t)nSp * nSp, sizeof(int));
+        w->NbInit = (int*)calloc(nSp, sizeof(int)); w->queue = (int*)calloc(nSp + 1, sizeof(int));
+        w->act = (unsigned char*)calloc(nSp, 1);
+    }
     /* seulex constructor */
     const double cpuFunc = 1, cpuJac = 5, cpuLU = 1, cpuSolve = 1;
     w->nSeq[0] = 2; w->nSeq[1] = 3;
@@ -186,7 +207,10 @@ static void ows_destroy(ows* w) {
     free(w->c_); free(w->dcdt_); free(w->cTp); free(w->dydx0); free(w->yTemp); free(w->k1); free(w->k2);
     free(w->k3); free(w->k4); free(w->err); free(w->dydx); free(w->dfdx); free(w->vv); free(w->y0);
     free(w->scale); free(w->ySeq); free(w->dy); free(w->yT); free(w->src); free(w->dfdy); free(w->a);
-    free(w->RRm); free(w->table); free(w->piv); free(w);
+    free(w->RRm); free(w->table); free(w->piv);
+    free(w->s2c); free(w->c2s); free(w->rdis); free(w->completeC); free(w->simplC); free(w->rABNum); free(w->PA);
+    free(w->CA); free(w->Rvalue); free(w->rABPos); free(w->rABOther); free(w->NbInit); free(w->queue); free(w->act);
+    free(w);
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -335,8 +359,12 @@ static void omega_all(ows* w, const double* c, double T, double* dcdt) {
     }
 }
 
+static void tdac_derivatives(ows* w, const double* y, double* dcdt);
+static void tdac_jacobian(ows* w, const double* y, double* dfdx, double* dfdc);
+
 /* StandardChemistryModel::derivatives(t, c, dcdt) */
 static void derivatives(ows* w, const double* y, double* dcdt) {
+    if (w->red) { tdac_derivatives(w, y, dcdt); return; }
     const oracle_mech* M = w->M;
     const int nSp = M->nSp;
     const double RR = w->O->o.gas_constant;
@@ -359,6 +387,7 @@ static void derivatives(ows* w, const double* y, double* dcdt) {
 
 /* StandardChemistryModel::jacobian(t, c, dcdt, dfdc); dcdt is the ODE solver's dfdx slot (quirk A.4) */
 static void jacobian(ows* w, const double* y, double* dfdx, double* dfdc) {
+    if (w->red) { tdac_jacobian(w, y, dfdx, dfdc); return; }
     const oracle_mech* M = w->M;
     const lbchem_mech_desc* d = &M->d;
     const int nSp = M->nSp, n = w->n;
@@ -421,6 +450,109 @@ static void jacobian(ows* w, const double* y, double* dfdx, double* dfdc) {
     for (int i = 0; i < nSp; ++i) dfdc[i * n + nSp] = 0.5 * (dfdc[i * n + nSp] - w->dcdt_[i]) / delta;
     dfdc[nSp * n + nSp] = 0;
     dfdc[(nSp + 1) * n + nSp] = 0;
+}
+
+
+/* ------------------------------------------------------------------------------------------------
+ * TDACChemistryModel::omega / derivatives / jacobian while a DAC-reduced mechanism is active
+ * (OpenFOAM v2306 chemistryModel/TDACChemistryModel/TDACChemistryModel.C, SURVEY A.12 [from memory]):
+ * the ODE vector is simplifiedC_ (NsDAC_ species, T, p); disabled reactions are skipped; rates, third-body
+ * sums, rho and cp use the COMPLETE concentration vector c_ (= completeC_ with the active entries replaced).
+ * ---------------------------------------------------------------------------------------------- */
+static void tdac_load_c(ows* w, const double* y) {
+    const int nSp = w->M->nSp;
+    for (int i = 0; i < nSp; ++i) w->c_[i] = w->completeC[i];
+    for (int i = 0; i < w->NsDAC; ++i) w->c_[w->s2c[i]] = fmax(y[i], 0.0);
+}
+
+static void tdac_omega_all(ows* w, const double* c, double T, double* dcdt) {
+    const oracle_mech* M = w->M;
+    const lbchem_mech_desc* d = &M->d;
+    for (int i = 0; i < w->n; ++i) dcdt[i] = 0;
+    for (int r = 0; r < M->nR; ++r) {
+        if (w->rdis[r]) continue;
+        double pf, cf, pr, cr; int lRef, rRef;
+        double om = omega_reaction(M, w->O, r, c, T, &pf, &cf, &lRef, &pr, &cr, &rRef);
+        for (int k = d->lhs_ptr[r]; k < d->lhs_ptr[r + 1]; ++k) dcdt[w->c2s[d->lhs_species[k]]] -= d->lhs_nu[k] * om;
+        for (int k = d->rhs_ptr[r]; k < d->rhs_ptr[r + 1]; ++k) dcdt[w->c2s[d->rhs_species[k]]] += d->rhs_nu[k] * om;
+    }
+}
+
+static void tdac_derivatives(ows* w, const double* y, double* dcdt) {
+    const oracle_mech* M = w->M;
+    const int nSp = M->nSp, Ns = w->NsDAC;
+    const double RR = w->O->o.gas_constant;
+    const double T = y[Ns];
+    w->cnt.n_rhs++;
+    tdac_load_c(w, y);
+    tdac_omega_all(w, w->c_, T, dcdt);
+    double rho = 0;
+    for (int i = 0; i < nSp; ++i) rho += M->d.W[i] * w->c_[i];
+    double cp = 0;
+    for (int i = 0; i < nSp; ++i) cp += w->c_[i] * (RR * janaf_cp(sp_coeffs(M, i, T), T));
+    cp /= rho;
+    double dT = 0;
+    for (int i = 0; i < Ns; ++i) { const int si = w->s2c[i]; dT += (RR * janaf_ha(sp_coeffs(M, si, T), T)) * dcdt[i]; }
+    dT /= rho * cp;
+    dcdt[Ns] = -dT;
+    dcdt[Ns + 1] = 0;
+}
+
+static void tdac_jacobian(ows* w, const double* y, double* dfdx, double* dfdc) {
+    const oracle_mech* M = w->M;
+    const lbchem_mech_desc* d = &M->d;
+    const int Ns = w->NsDAC, n = w->n;
+    const int* c2s = w->c2s;
+    const double T = y[Ns];
+    double* c = w->c_;
+    w->cnt.n_jac++;
+    tdac_load_c(w, y);
+    memset(dfdc, 0, sizeof(double) * n * n);
+    /* the dfdx slot: same option as the standard model (irrelevant for seulex, which never reads it) */
+    tdac_omega_all(w, c, T, dfdx);
+    if (!w->O->o.dfdx_is_dcdt) for (int i = 0; i < n; ++i) dfdx[i] = 0;
+    for (int r = 0; r < M->nR; ++r) {
+        if (w->rdis[r]) continue;
+        const double kf0 = reaction_kf(M, r, T, c);
+        const double kr0 = reaction_kr(M, w->O, r, kf0, T);
+        const int l0 = d->lhs_ptr[r], l1 = d->lhs_ptr[r + 1];
+        const int r0 = d->rhs_ptr[r], r1 = d->rhs_ptr[r + 1];
+        for (int j = l0; j < l1; ++j) {
+            const int sj = c2s[d->lhs_species[j]];
+            double kf = kf0;
+            for (int i = l0; i < l1; ++i) {
+                const int si = d->lhs_species[i];
+                const double el = d->lhs_exp[i];
+                if (i == j) {
+                    if (el < 1.0) { if (c[si] > O_SMALL) kf *= el * pow(c[si] + O_VSMALL, el - 1.0); else kf = 0.0; }
+                    else kf *= el * pow(c[si], el - 1.0);
+                } else kf *= pow(c[si], el);
+            }
+            for (int i = l0; i < l1; ++i) dfdc[c2s[d->lhs_species[i]] * n + sj] -= d->lhs_nu[i] * kf;
+            for (int i = r0; i < r1; ++i) dfdc[c2s[d->rhs_species[i]] * n + sj] += d->rhs_nu[i] * kf;
+        }
+        for (int j = r0; j < r1; ++j) {
+            const int sj = c2s[d->rhs_species[j]];
+            double kr = kr0;
+            for (int i = r0; i < r1; ++i) {
+                const int si = d->rhs_species[i];
+                const double er = d->rhs_exp[i];
+                if (i == j) {
+                    if (er < 1.0) { if (c[si] > O_SMALL) kr *= er * pow(c[si] + O_VSMALL, er - 1.0); else kr = 0.0; }
+                    else kr *= er * pow(c[si], er - 1.0);
+                } else kr *= pow(c[si], er);
+            }
+            for (int i = l0; i < l1; ++i) dfdc[c2s[d->lhs_species[i]] * n + sj] += d->lhs_nu[i] * kr;
+            for (int i = r0; i < r1; ++i) dfdc[c2s[d->rhs_species[i]] * n + sj] -= d->rhs_nu[i] * kr;
+        }
+    }
+    const double delta = 1.0e-3;
+    tdac_omega_all(w, c, T + delta, w->dcdt_);
+    for (int i = 0; i < Ns; ++i) dfdc[i * n + Ns] = w->dcdt_[i];
+    tdac_omega_all(w, c, T - delta, w->dcdt_);
+    for (int i = 0; i < Ns; ++i) dfdc[i * n + Ns] = 0.5 * (dfdc[i * n + Ns] - w->dcdt_[i]) / delta;
+    dfdc[Ns * n + Ns] = 0;
+    dfdc[(Ns + 1) * n + Ns] = 0;
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -785,7 +917,7 @@ static void ode_solve(ows* w, double xStart, double xEnd, double* y, double* dxT
  * chemistrySolver::solve(c, T, p, deltaT, subDeltaT): ode<> and EulerImplicit<>
  * ---------------------------------------------------------------------------------------------- */
 static void ode_chem_solve(ows* w, double* c, double* T, double* p, double* deltaT, double* subDeltaT) {
-    const int nSp = w->M->nSp;
+    const int nSp = w->n - 2;   /* this->nSpecie(): NsDAC_ while a reduced mechanism is active (ode::solve resizes cTp_) */
     for (int i = 0; i < nSp; ++i) w->cTp[i] = c[i];
     w->cTp[nSp] = *T;
     w->cTp[nSp + 1] = *p;
@@ -913,6 +1045,140 @@ static void solve_cell(ows* w, const double* Y, int64_t ldy, int64_t cell, doubl
     }
 }
 
+
+/* ------------------------------------------------------------------------------------------------
+ * chemistryReductionMethods::DAC::reduceMechanism(c, T, p), automaticSIS off
+ * (OpenFOAM v2306 chemistryModel/TDACChemistryModel/reduction/DAC/DAC.C, SURVEY A.12 [from memory]; called at
+ * reference LoadBalancedTDACChemistryModel.C:388). Per reaction: omega_i; per species A of the reaction the net
+ * nu_A * omega_i (a species on both sides is counted once, summed); P_A / C_A = sums of the positive / negative
+ * contributions; numerators of r_AB (signed sums over the reactions that hold both A and B) are stored per A in
+ * first-appearance order of B. Breadth-first search from the initial set with R(seed) = 1; an edge is followed
+ * when R_u * min(|num_AB| / max(P_A, C_A), 1) >= tolerance, R_B = max(R_B, R_u r_AB); a species is queued once.
+ * Reactions touching an inactive species are disabled; the simplified ordering is ascending complete index.
+ * ---------------------------------------------------------------------------------------------- */
+static void dac_reduce(ows* w, const double* c, double T) {
+    const oracle_mech* M = w->M;
+    const lbchem_mech_desc* d = &M->d;
+    const int nSp = M->nSp, nR = M->nR;
+    for (int i = 0; i < nSp; ++i) { w->completeC[i] = c[i]; w->PA[i] = 0; w->CA[i] = 0; w->NbInit[i] = 0; w->Rvalue[i] = 0; w->act[i] = 0; }
+    for (int i = 0; i < nSp * nSp; ++i) { w->rABPos[i] = -1; w->rABOther[i] = -1; w->rABNum[i] = 0; }
+    for (int r = 0; r < nR; ++r) {
+        double pf, cf, pr, cr; int lRef, rRef;
+        const double omegai = omega_reaction(M, w->O, r, c, T, &pf, &cf, &lRef, &pr, &cr, &rRef);
+        double wA[2 * MAXSIDE]; int wAID[2 * MAXSIDE]; int nw = 0;
+        for (int k = d->lhs_ptr[r]; k < d->lhs_ptr[r + 1]; ++k) {
+            const int ss = d->lhs_species[k]; const double sl = -d->lhs_nu[k];
+            int found = 0;
+            for (int id = 0; id < nw; ++id) if (wAID[id] == ss) { wA[id] += sl * omegai; found = 1; break; }
+            if (!found) { wA[nw] = sl * omegai; wAID[nw++] = ss; }
+        }
+        for (int k = d->rhs_ptr[r]; k < d->rhs_ptr[r + 1]; ++k) {
+            const int ss = d->rhs_species[k]; const double sl = d->rhs_nu[k];
+            int found = 0;
+            for (int id = 0; id < nw; ++id) if (wAID[id] == ss) { wA[id] += sl * omegai; found = 1; break; }
+            if (!found) { wA[nw] = sl * omegai; wAID[nw++] = ss; }
+        }
+        for (int id = 0; id < nw; ++id) {
+            const int A = wAID[id];
+            /* the other species of this reaction, each once, in lhs-then-rhs order (the FIFO of the reference) */
+            for (int side = 0; side < 2; ++side) {
+                const int k0 = side ? d->rhs_ptr[r] : d->lhs_ptr[r], k1 = side ? d->rhs_ptr[r + 1] : d->lhs_ptr[r + 1];
+                const int32_t* sp = side ? d->rhs_species : d->lhs_species;
+                for (int k = k0; k < k1; ++k) {
+                    const int B = sp[k];
+                    if (B == A) continue;
+                    int seen = 0;   /* deltaBi: count B once per (reaction, A) */
+                    for (int s2 = 0; s2 < 2 && !seen; ++s2) {
+                        const int q0 = s2 ? d->rhs_ptr[r] : d->lhs_ptr[r];
+                        const int q1 = (s2 == side) ? k : (s2 ? d->rhs_ptr[r + 1] : d->lhs_ptr[r + 1]);
+                        if (s2 > side) break;
+                        const int32_t* sq = s2 ? d->rhs_species : d->lhs_species;
+                        for (int q = q0; q < q1; ++q) if (sq[q] == B) { seen = 1; break; }
+                    }
+                    if (seen) continue;
+                    if (w->rABPos[A * nSp + B] == -1) {
+                        const int pos = w->NbInit[A]++;
+                        w->rABPos[A * nSp + B] = pos;
+                        w->rABNum[A * nSp + pos] = wA[id];
+                        w->rABOther[A * nSp + pos] = B;
+                    } else {
+                        w->rABNum[A * nSp + w->rABPos[A * nSp + B]] += wA[id];
+                    }
+                }
+            }
+            if (wA[id] > 0.0) w->PA[A] += wA[id]; else w->CA[A] += -wA[id];
+        }
+    }
+    /* search from the initial set */
+    int head = 0, tail = 0, nActive = 0;
+    for (int i = 0; i < w->O->dac_ninit; ++i) {
+        const int q = w->O->dac_init[i];
+        if (q < 0 || q >= nSp || w->act[q]) continue;
+        w->act[q] = 1; nActive++; w->queue[tail++] = q; w->Rvalue[q] = 1.0;
+    }
+    const double tol = w->O->dac_tol;
+    while (head < tail) {
+        const int u = w->queue[head++];
+        const double Den = fmax(w->PA[u], w->CA[u]);
+        if (Den > O_VSMALL) {
+            for (int v = 0; v < w->NbInit[u]; ++v) {
+                const int other = w->rABOther[u * nSp + v];
+                double rAB = fabs(w->rABNum[u * nSp + v]) / Den;
+                if (rAB > 1) rAB = 1;
+                const double Rt = w->Rvalue[u] * rAB;
+                if (Rt >= tol) {
+                    if (Rt > w->Rvalue[other]) w->Rvalue[other] = Rt;
+                    if (!w->act[other]) { w->act[other] = 1; nActive++; w->queue[tail++] = other; }
+                }
+            }
+        }
+    }
+    for (int r = 0; r < nR; ++r) {
+        int dis = 0;
+        for (int k = d->lhs_ptr[r]; k < d->lhs_ptr[r + 1] && !dis; ++k) if (!w->act[d->lhs_species[k]]) dis = 1;
+        for (int k = d->rhs_ptr[r]; k < d->rhs_ptr[r + 1] && !dis; ++k) if (!w->act[d->rhs_species[k]]) dis = 1;
+        w->rdis[r] = (unsigned char)dis;
+    }
+    int j = 0;
+    for (int i = 0; i < nSp; ++i) {
+        if (w->act[i]) { w->s2c[j] = i; w->simplC[j] = c[i]; w->c2s[i] = j++; } else w->c2s[i] = -1;
+    }
+    w->NsDAC = nActive;
+}
+
+/* LoadBalancedTDACChemistryModel::solveCell with mechRed()->active() (reference LoadBalancedTDACChemistryModel.C:360-435).
+ * The reduced call passes cData.T() for BOTH T and p (:406-409): p is dead for perfectGas, and on return the aliased
+ * reference is first set to the final temperature and then overwritten by the p slot (= the initial T), so the cell
+ * temperature comes back unchanged. Reproduced here by passing the same pointer twice. */
+static void solve_cell_tdac(ows* w, const double* Y, int64_t ldy, int64_t cell, double* T, double* p, double rho,
+                            double deltaT, double* deltaTChem, double* RR, int32_t* status, int32_t* nActive) {
+    const oracle_mech* M = w->M;
+    const int nSp = M->nSp;
+    const int nFull = w->n;
+    (void)p;
+    w->fail = 0;
+    double c0[nSp], c[nSp];
+    for (int i = 0; i < nSp; ++i) { c[i] = rho * Y[i * ldy + cell] / M->d.W[i]; c0[i] = c[i]; }
+    dac_reduce(w, c, *T);
+    if (nActive) *nActive = w->NsDAC;
+    w->red = 1; w->n = w->NsDAC + 2;
+    double timeLeft = deltaT;
+    int guard = 0;
+    while (timeLeft > O_SMALL) {
+        double dt = timeLeft;
+        for (int i = 0; i < nSp; ++i) w->completeC[i] = c[i];
+        ode_chem_solve(w, w->simplC, T, T, &dt, deltaTChem);
+        for (int i = 0; i < w->NsDAC; ++i) c[w->s2c[i]] = w->simplC[i];
+        if (w->fail) break;
+        timeLeft -= dt;
+        if (++guard > 10000000) { w->fail = LBCHEM_CELL_MAX_STEPS; break; }
+    }
+    w->red = 0; w->n = nFull;
+    /* the TDAC variant has no deltaTChemMax clip in solveCell; RR as in its solve<DeltaT> (:905-915) */
+    for (int i = 0; i < nSp; ++i) RR[i * ldy + cell] = (c[i] - c0[i]) * M->d.W[i] / deltaT;
+    *status = w->fail ? w->fail : LBCHEM_CELL_OK;
+}
+
 static double now_s(void) {
     struct timespec ts;
     clock_gettime(CLOCK_MONOTONIC, &ts);
@@ -930,6 +1196,7 @@ typedef struct {
     int64_t lo, hi, ldy;
     const double *Y, *T, *p, *rho, *deltaT; double deltaT_uniform;
     double *deltaTChem, *RR, *Tout, *cpu_time, *attempts; int32_t* status;
+    int32_t* nActive;      /* DAC: NsDAC_ per cell */
     int64_t cnt[6];
 } batch_job;
 
@@ -941,6 +1208,10 @@ static void* batch_worker(void* arg) {
         double Tc = j->T[cidx], pc = j->p[cidx];
         int32_t st = 0;
         double t0 = now_s();
+        if (j->O->dac_active)
+            solve_cell_tdac(w, j->Y, j->ldy, cidx, &Tc, &pc, j->rho[cidx], j->deltaT ? j->deltaT[cidx] : j->deltaT_uniform,
+                            &j->deltaTChem[cidx], j->RR, &st, j->nActive ? &j->nActive[cidx] : NULL);
+        else
         solve_cell(w, j->Y, j->ldy, cidx, &Tc, &pc, j->rho[cidx], j->deltaT ? j->deltaT[cidx] : j->deltaT_uniform,
                    &j->deltaTChem[cidx], j->RR, &st);
         double t1 = now_s();
@@ -955,14 +1226,40 @@ static void* batch_worker(void* arg) {
     return NULL;
 }
 
+/* reduction{} for the batches that follow (process-wide; the tests set it and reset it around a call) */
+static struct { int active; double tol; int ninit; int init[64]; int32_t* nActive; } g_dac;
+void oracle_set_reduction(int active, double tol, int n_init, const int32_t* init_species, int32_t* n_active_out) {
+    g_dac.active = active; g_dac.tol = tol; g_dac.ninit = n_init > 64 ? 64 : n_init;
+    for (int i = 0; i < g_dac.ninit; ++i) g_dac.init[i] = init_species[i];
+    g_dac.nActive = n_active_out;
+}
+
+/* probe: the active-species flags DAC gives for one state (c[nSp] in kmol/m3, T) */
+int oracle_dac_reduce(const oracle_mech* M, const lbchem_options* opts, double tol, int n_init, const int32_t* init_species,
+                      const double* c, double T, int32_t* active_out, int32_t* disabled_out) {
+    oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;
+    O.dac_active = 1; O.dac_tol = tol; O.dac_ninit = n_init > 64 ? 64 : n_init;
+    for (int i = 0; i < O.dac_ninit; ++i) O.dac_init[i] = init_species[i];
+    ows* w = ows_create(M, &O);
+    dac_reduce(w, c, T);
+    for (int i = 0; i < M->nSp; ++i) active_out[i] = w->act[i];
+    if (disabled_out) for (int r = 0; r < M->nR; ++r) disabled_out[r] = w->rdis[r];
+    const int ns = w->NsDAC;
+    ows_destroy(w);
+    return ns;
+}
+
 int oracle_solve_batch(const oracle_mech* M, const lbchem_options* opts, int seulex_errold_max, int64_t n,
                        int64_t ldy, const double* Y, const double* T, const double* p, const double* rho,
                        const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR,
                        double* Tout, double* cpu_time, double* attempts, int32_t* status, int64_t* counters,
                        int nthreads) {
     oracle_opts O;
+    memset(&O, 0, sizeof(O));
     O.o = *opts;
     O.seulex_errold_max = seulex_errold_max;
+    O.dac_active = g_dac.active; O.dac_tol = g_dac.tol; O.dac_ninit = g_dac.ninit;
+    memcpy(O.dac_init, g_dac.init, sizeof(O.dac_init));
     if (nthreads < 1) nthreads = 1;
     if (nthreads > 256) nthreads = 256;
     batch_job jobs[256];
@@ -974,7 +1271,7 @@ int oracle_solve_batch(const oracle_mech* M, const lbchem_options* opts, int seu
         j->lo = n * t / nthreads; j->hi = n * (t + 1) / nthreads;
         j->Y = Y; j->T = T; j->p = p; j->rho = rho; j->deltaT = deltaT; j->deltaT_uniform = deltaT_uniform;
         j->deltaTChem = deltaTChem; j->RR = RR; j->Tout = Tout; j->cpu_time = cpu_time; j->attempts = attempts;
-        j->status = status;
+        j->status = status; j->nActive = g_dac.active ? g_dac.nActive : NULL;
         if (t > 0) pthread_create(&th[t], NULL, batch_worker, j);
     }
     batch_worker(&jobs[0]);
@@ -988,19 +1285,19 @@ int oracle_solve_batch(const oracle_mech* M, const lbchem_options* opts, int seu
 
 /* probes used by the tests: RHS and Jacobian of one state (y = c[nSp], T, p) */
 void oracle_derivatives(const oracle_mech* M, const lbchem_options* opts, const double* y, double* dydt) {
-    oracle_opts O; O.o = *opts; O.seulex_errold_max = 0;
+    oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;
     ows* w = ows_create(M, &O);
     derivatives(w, y, dydt);
     ows_destroy(w);
 }
 void oracle_jacobian(const oracle_mech* M, const lbchem_options* opts, const double* y, double* dfdx, double* dfdy) {
-    oracle_opts O; O.o = *opts; O.seulex_errold_max = 0;
+    oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;
     ows* w = ows_create(M, &O);
     jacobian(w, y, dfdx, dfdy);
     ows_destroy(w);
 }
 void oracle_rates(const oracle_mech* M, const lbchem_options* opts, const double* c, double T, double* kf, double* kr) {
-    oracle_opts O; O.o = *opts; O.seulex_errold_max = 0;
+    oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;
     for (int r = 0; r < M->nR; ++r) { kf[r] = reaction_kf(M, r, T, c); kr[r] = reaction_kr(M, &O, r, kf[r], T); }
 }
 int oracle_lu_solve(int m, double* A, double* b) {

@@ -50,6 +50,10 @@ def lib() -> C.CDLL:
         L.oracle_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
         L.oracle_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
         L.oracle_cells_to_send.restype = C.c_int32
+        L.oracle_set_reduction.argtypes = [C.c_int, C.c_double, C.c_int, _ip, _ip]
+        L.oracle_set_reduction.restype = None
+        L.oracle_dac_reduce.argtypes = [C.c_void_p, C.POINTER(Options), C.c_double, C.c_int, _ip, _dp, C.c_double, _ip, _ip]
+        L.oracle_dac_reduce.restype = C.c_int
         _lib = L
     return _lib
 
@@ -64,6 +68,20 @@ class OracleModel:
         self.options = options or default_options()
         self.seulex_errold_max = int(seulex_errold_max)
         self.counters = None
+        self.reduction = None          # (tolerance, [initial-set species indices]) = reduction{active on; method DAC; ...}
+
+    def set_reduction(self, tolerance=None, initial_set=None):
+        """DAC as LoadBalancedTDAC runs it (reference LoadBalancedTDACChemistryModel.C:385-393); None switches it off."""
+        self.reduction = None if tolerance is None else (float(tolerance), [int(i) for i in initial_set])
+
+    def dac_reduce(self, c, T, tolerance, initial_set):
+        """Active-species flags [nSp] and disabled-reaction flags [nR] DAC gives for one state."""
+        c = np.ascontiguousarray(c, dtype=np.float64)
+        init = np.ascontiguousarray(initial_set, dtype=np.int32)
+        act = np.zeros(self.mech.n_species, np.int32); dis = np.zeros(self.mech.n_reactions, np.int32)
+        lib().oracle_dac_reduce(self.h, C.byref(self.options), float(tolerance), len(init), _as_ip(init), _as_dp(c),
+                                float(T), _as_ip(act), _as_ip(dis))
+        return act.astype(bool), dis.astype(bool)
 
     def __del__(self):
         try:
@@ -88,16 +106,27 @@ class OracleModel:
         RR = np.zeros_like(Y); Tout = np.zeros(n); cpu = np.zeros(n); att = np.zeros(n)
         status = np.zeros(n, np.int32)
         cnt = (C.c_int64 * 6)()
-        rc = lib().oracle_solve_batch(
-            self.h, C.byref(self.options), self.seulex_errold_max, n, n, _as_dp(Y), _as_dp(T), _as_dp(p),
-            _as_dp(rho), _as_dp(dT_arr), dT_u, _as_dp(dtc), _as_dp(RR), _as_dp(Tout), _as_dp(cpu), _as_dp(att),
-            _as_ip(status), cnt, int(nthreads),
-        )
+        n_active = np.full(n, nSp, np.int32)
+        if self.reduction is not None:
+            init = np.ascontiguousarray(self.reduction[1], dtype=np.int32)
+            lib().oracle_set_reduction(1, self.reduction[0], len(init), _as_ip(init), _as_ip(n_active))
+        try:
+            rc = self._call(n, Y, T, p, rho, dT_arr, dT_u, dtc, RR, Tout, cpu, att, status, cnt, nthreads)
+        finally:
+            if self.reduction is not None:
+                lib().oracle_set_reduction(0, 0.0, 0, None, None)
         assert rc == 0
         names = ["n_steps", "n_attempts", "n_jac", "n_lu", "n_solve", "n_rhs"]
         self.counters = {k: int(v) for k, v in zip(names, cnt)}
         return dict(RR=RR, T=Tout, deltaTChem=dtc, cpu_time=cpu, attempts=att, status=status,
-                    counters=self.counters)
+                    counters=self.counters, n_active=n_active)
+
+    def _call(self, n, Y, T, p, rho, dT_arr, dT_u, dtc, RR, Tout, cpu, att, status, cnt, nthreads):
+        return lib().oracle_solve_batch(
+            self.h, C.byref(self.options), self.seulex_errold_max, n, n, _as_dp(Y), _as_dp(T), _as_dp(p),
+            _as_dp(rho), _as_dp(dT_arr), dT_u, _as_dp(dtc), _as_dp(RR), _as_dp(Tout), _as_dp(cpu), _as_dp(att),
+            _as_ip(status), cnt, int(nthreads),
+        )
 
     def derivatives(self, y):
         y = np.ascontiguousarray(y, dtype=np.float64)

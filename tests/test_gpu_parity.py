@@ -216,3 +216,40 @@ def test_driver_on_one_gpu_equals_direct_call(gri, flame):
     direct2 = chem.solve_host(Y, T, p, rho, DT, direct["deltaTChem"])
     assert np.array_equal(model.RR.cpu().numpy(), direct2["RR"])
     chem.close()
+
+
+# ---- LoadBalancedTDAC with DAC reduction (BASELINE config 5) ------------------------
+DAC_TOL = 1e-4                      # tests/Cases/Case-chemistry/constant/chemistryProperties:46
+DAC_INIT = ("CO", "CH4", "HO2")     # initialSet, chemistryProperties:52-57
+
+
+@pytest.mark.parametrize("solver,rel_tol", [("seulex", 1e-1), ("Rosenbrock34", 1e-2)])
+def test_gri_flame_fixture_dac_parity(gri, flame, solver, rel_tol):
+    """All 4000 fixture cells with `reduction{active on; method DAC; tolerance 1e-4; initialSet CO CH4 HO2}`:
+    the kernel integrates the reduced system embedded in the full index space (removed species' rows and columns
+    skipped), the oracle integrates the genuinely reduced NsDAC_+2 system as TDACChemistryModel does. Same active
+    sets cell by cell, RR / deltaTChem within 1e-6, temperature returned unchanged (reference T/p aliasing)."""
+    sel = np.arange(flame["T"].shape[0])
+    Y, T, p, rho = _state(gri, flame, sel)
+    init = [list(gri.species).index(s) for s in DAC_INIT]
+    opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol)
+    chem = capi.Chemistry(gri, opts)
+    chem.set_reduction(DAC_TOL, init)
+    got = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+    ns_gpu = chem.active_species(T.size)
+    st = chem.stats()
+    om = O.OracleModel(gri, opts)
+    om.set_reduction(DAC_TOL, init)
+    ref = om.solve_batch(Y, T, p, rho, DT, DTCHEM, nthreads=8)
+    print(solver, "NsDAC min/mean/max", ns_gpu.min(), ns_gpu.mean(), ns_gpu.max(), "gpu stats", st, "oracle", ref["counters"])
+    # a species whose path value sits within round-off of the tolerance may flip: none expected on this fixture
+    assert (ns_gpu == ref["n_active"]).all(), np.nonzero(ns_gpu != ref["n_active"])[0][:10]
+    assert ns_gpu.min() >= len(init) and ns_gpu.max() < gri.n_species
+    assert np.array_equal(got["T"], T) and np.array_equal(ref["T"], T)
+    _compare(gri, Y, rho, got, ref, DT, f"gri-dac/{solver}")
+    # switching the reduction off again gives the full-mechanism result
+    chem.set_reduction(None)
+    full = chem.solve_host(Y[:, :256], T[:256], p[:256], rho[:256], DT, DTCHEM)
+    ref_full = O.OracleModel(gri, opts).solve_batch(Y[:, :256], T[:256], p[:256], rho[:256], DT, DTCHEM, nthreads=8)
+    _compare(gri, Y[:, :256], rho[:256], full, ref_full, DT, f"gri-dac-off/{solver}")
+    chem.close()
