@@ -43,7 +43,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", type=int, default=1_000_000, help="cells per GPU")
     ap.add_argument("--solver", default="seulex", choices=list(SOLVERS))
-    ap.add_argument("--workload", default="gri_uniform", choices=["gri_uniform", "gri_skewed"])
+    ap.add_argument("--workload", default="gri_uniform", choices=["gri_uniform", "gri_skewed", "gri_dac", "gri_tiled"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="cells in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -56,14 +56,32 @@ def make_workload(name, n, rank, world=1):
     from loadbalancedchemistrymodel_b200 import workloads as W
     if name == "gri_skewed":
         return W.gri_skewed(n, rank=rank, world=world)
+    if name in ("gri_dac", "gri_tiled"):
+        return W.gri_tiled(n, rank=rank)
     return W.gri_uniform(n, rank=rank)
+
+
+DAC_TOL, DAC_INIT = 1e-4, ("CO", "CH4", "HO2")   # reference tests/Cases/Case-chemistry/constant/chemistryProperties:46,52-57
+
+
+def dac_initial_set(mech):
+    return [list(mech.species).index(s) for s in DAC_INIT]
+
+
+WORKLOAD_TEXT = {
+    "gri_uniform": "BASELINE config 3; fixture cells T>1500 K resampled + noise, seed 1003",
+    "gri_skewed": "BASELINE config 4; hot cells (T>1500 K) contiguous at the start of the global index space, cold cells T<350 K, seed 1004",
+    "gri_tiled": "BASELINE config 5 input without the reduction: the unfiltered 4000-cell fixture tiled + noise, seed 1005",
+    "gri_dac": "BASELINE config 5; the unfiltered 4000-cell fixture tiled + noise, seed 1005; reduction{active on; method DAC; "
+               "tolerance 1e-4; initialSet CO CH4 HO2}, tabulation off",
+}
 
 
 def config_dict(args, n_gpus, extra=None):
     s, atol, rtol = SOLVERS[args.solver]
     cfg = {
         "workload": f"{args.workload}: GRI-Mech 3.0 (53 species, 325 reactions), {args.cells} synthetic cells per GPU "
-                    f"({"BASELINE config 3; fixture cells T>1500 K resampled + noise, seed 1003" if args.workload == "gri_uniform" else "BASELINE config 4; hot cells (T>1500 K) contiguous at the start of the global index space, cold cells T<350 K, seed 1004"})",
+                    f"({WORKLOAD_TEXT[args.workload]})",
         "mechanism": "GRI-3.0", "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
         "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; per step: all-gather of the cost, bit-exact plan, NCCL p2p forward/return of planned cells (model.py)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
         "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
@@ -82,6 +100,8 @@ def cpu_oracle_rate(args, n_sample, nthreads, steps=1, warmup=0):
     s, atol, rtol = SOLVERS[args.solver]
     mech, Y, T, p, rho = make_workload(args.workload, n_sample, rank=0)
     om = O.OracleModel(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol))
+    if args.workload == "gri_dac":
+        om.set_reduction(DAC_TOL, dac_initial_set(mech))
     for _ in range(warmup):
         om.solve_batch(Y, T, p, rho, 1e-6, 1e-7, nthreads=nthreads)
     t0 = time.perf_counter()
@@ -175,6 +195,8 @@ def run_b200(args):
     mech, Y, T, p, rho = make_workload(args.workload, n, rank, world)
     nSp = mech.n_species
     chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol), device=local)
+    if args.workload == "gri_dac":
+        chem.set_reduction(DAC_TOL, dac_initial_set(mech))
 
     def pinned(a):
         t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
@@ -296,7 +318,8 @@ def run_b200(args):
             "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
             "kernel": "v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)", "kernel_ms": k_ms,
             "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
-            "flops_per_cell": flops / n, "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts",
+            "flops_per_cell": flops / n, "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts"
+                          + (" at the FULL system size n = 55 (upper bound: the reduced systems are smaller)" if args.workload == "gri_dac" else ""),
             "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
                     "bytes_per_cell": 912, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
         }
