@@ -115,7 +115,7 @@ struct Ctx {
     const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
-enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N };
+enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N, CNT_NODE = 7 };   // CNT_NODE: equations of the ODE system (NsDAC_+2 when reduced)
 
 __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
@@ -187,6 +187,7 @@ __device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* bas
 
 // omega of every reaction at (CC, T) into OM[pos]; keep != 0 also stores kf, kr (Jacobian assembly).
 // Pass structure (one exp call site): exponentials -> fall-off blending -> kf, kr, mass action.
+template <bool DAC>
 __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int keep, double T, double lnT, double invT) {
     const Grp g(base);
     const SMech& S = cx->S;
@@ -195,7 +196,7 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
     const double *GL = WS(GL), *GH = WS(GH), *ME = WS(ME), *CC = WS(CC);
     // DAC: reactions touching a removed species are skipped (TDACChemistryModel::omega, reactionsDisabled_)
     const unsigned long long* MSK = reinterpret_cast<const unsigned long long*>(WS(MSK));
-    const bool dac = cx->dac != nullptr;
+    constexpr bool dac = DAC;
 #define RX_OFF(p) (dac && ((MSK[(p) >> 6] >> ((p) & 63)) & 1ull))
     // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
 #pragma unroll 1
@@ -319,6 +320,7 @@ __device__ __forceinline__ void finish_derivatives(const Grp& g, const Ctx* cx, 
 }
 
 // StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
+template <bool DAC>
 __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
     const Grp g(base);
     const SMech& S = cx->S;
@@ -327,12 +329,13 @@ __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const doub
     const double T = y[nSp];
     const double lnT = log(T), invT = 1.0 / T;
     prepare(g, cx, base, y, T, lnT, true);
-    reaction_sweep(cx, base, 0, T, lnT, invT);
+    reaction_sweep<DAC>(cx, base, 0, T, lnT, invT);
     finish_derivatives(g, cx, base, T, t < nSp ? gather_species(S, WS(OM), t) : 0.0, dydt);
 }
 
 // StandardChemistryModel::jacobian (A.9) into the sparse store: JS[entry] (species block, structural
 // non-zeros in (row, col) order), JT[i] = d(dc_i/dt)/dT by central difference; dfdx = species rates (A.4 quirk)
+template <bool DAC>
 __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx, double* dydt0) {
     const Grp g(base);
     const SMech& S = cx->S;
@@ -346,7 +349,7 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
         const double Tp = pass == 0 ? T : (pass == 1 ? T + delta : T - delta);
         const double lnT = log(Tp), invT = 1.0 / Tp;
         prepare(g, cx, base, y, Tp, lnT, pass == 0);
-        reaction_sweep(cx, base, pass == 0, Tp, lnT, invT);
+        reaction_sweep<DAC>(cx, base, pass == 0, Tp, lnT, invT);
         if (pass == 0) {
             // species rates at (y, T): the dfdx slot (A.4 quirk) and, on request, the full derivatives() at the same state
             // (adaptiveSolver's dydx0: the reference evaluates it separately from the same rates)
@@ -393,6 +396,16 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_JAC]++;
 }
 
+// DAC: columns of kept species only. First set bit of `act` at index >= j (nSp when none) / last set bit at index <= j (-1 when none)
+__device__ __forceinline__ int next_col(unsigned long long act, int j, int nSp) {
+    const unsigned long long r = act & (~0ull << j);
+    return r ? __ffsll((long long)r) - 1 : nSp;
+}
+__device__ __forceinline__ int prev_col(unsigned long long act, int j) {
+    const unsigned long long r = act & ((2ull << j) - 1ull);
+    return r ? 63 - __clzll((long long)r) : -1;
+}
+
 // ------------------------------------------------------------------------------------------------
 // dense linear algebra on the shared-memory matrix: thread t owns species row t of  dg*I - J
 // (columns 0..nSp: species block + temperature column). The T and p rows are (0 .. dg .. 0): handled in closed form.
@@ -400,6 +413,7 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
 // Build the matrix from the sparse Jacobian and factorise it: LUDecompose (A.10) with implicit row scaling and
 // partial pivoting. Rows never move: `pos` is the index the row would have in the reference's physically swapped
 // matrix (drives its tie rule: the LAST maximal row wins), STEP[t] the column at which row t became the pivot row.
+template <bool DAC>
 __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const Grp g(base);
     const SMech& S = cx->S;
@@ -437,13 +451,12 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const double vv = 1.0 / big;
     // DAC: the rows and columns of removed species hold only the diagonal dg (no reaction touches them), i.e. the reduced
     // system of the reference embedded in the full index space: such a row is its own pivot row and its column is skipped
-    const unsigned long long act = cx->dac ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(S.nR + 63) >> 6] : ~0ull;
+    const unsigned long long act = DAC ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(S.nR + 63) >> 6] : ~0ull;
     bool done = (t >= nSp) || !((act >> t) & 1ull);
     int pos = t;
     if (done && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
 #pragma unroll 1
-    for (int j = 0; j < nSp; ++j) {
-        if (!((act >> j) & 1ull)) continue;
+    for (int j = DAC ? next_col(act, 0, nSp) : 0; j < nSp; j = DAC ? next_col(act, j + 1, nSp) : j + 1) {
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
         const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
@@ -500,6 +513,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
 }
 
 // x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out)
+template <bool DAC>
 __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     const Grp g(base);
     const int nSp = cx->S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
@@ -509,13 +523,12 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     g.sync();
     const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
     double bt = t < N ? x[t] : 0.0;
-    const unsigned long long act = cx->dac ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(cx->S.nR + 63) >> 6] : ~0ull;
+    const unsigned long long act = DAC ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(cx->S.nR + 63) >> 6] : ~0ull;
     const bool sp = t < nSp && ((act >> t) & 1ull);
     if (t < nSp && !sp) x[t] = bt * RD[t];          // removed species: decoupled diagonal row
     // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
-    for (int j = 0; j < nSp; ++j) {
-        if (!((act >> j) & 1ull)) continue;
+    for (int j = DAC ? next_col(act, 0, nSp) : 0; j < nSp; j = DAC ? next_col(act, j + 1, nSp) : j + 1) {
         if (step == j) BS[j] = bt;
         g.sync();
         if (sp && step > j) bt = fma(-row[j], BS[j], bt);
@@ -526,8 +539,7 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     g.sync();
     if (sp) bt = fma(-row[nSp], BS[nSp], bt);
 #pragma unroll 1
-    for (int j = nSp - 1; j >= 0; --j) {
-        if (!((act >> j) & 1ull)) continue;
+    for (int j = DAC ? prev_col(act, nSp - 1) : nSp - 1; j >= 0; j = DAC ? (j > 0 ? prev_col(act, j - 1) : -1) : j - 1) {
         if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
         g.sync();
         if (sp && step < j) bt = fma(-row[j], BS[j], bt);
@@ -556,7 +568,7 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
     const double T = y[nSp];
     const double lnT = log(T), invT = 1.0 / T;
     prepare(g, cx, base, y, T, lnT, true);
-    reaction_sweep(cx, base, 0, T, lnT, invT);
+    reaction_sweep<true>(cx, base, 0, T, lnT, invT);
     const double* OM = WS(OM);
     double* NUM = WS(A);
     double *PA = VEC(1), *CA = VEC(2), *RV = VEC(3);
@@ -655,7 +667,7 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
 // ------------------------------------------------------------------------------------------------
 // integrators (control flow identical to lbchem_kernels_v2.cu; only the heavy routines are calls)
 // ------------------------------------------------------------------------------------------------
-struct Cell { int fail; double theta; int kTarg; int f0valid; int nOde; };   // nOde: equations of the ODE system (NsDAC_+2 when reduced)
+struct Cell { int fail; double theta; int kTarg; int f0valid; };
 struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
 
 __constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
@@ -665,6 +677,7 @@ __constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434
 
 // one Rosenbrock34 attempt (A.4) from Y0=V0 with step dx; result in V1. The sparse Jacobian (and dfdx in V3)
 // of the step start are re-used after a rejected attempt: the reference recomputes identical values.
+template <bool DAC>
 __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dx) {
     const double a21 = 2, a31 = 48.0 / 25.0, a32 = 6.0 / 25.0, c21 = -8, c31 = 372.0 / 25.0, c32 = 12.0 / 5.0,
                  c41 = -112.0 / 125.0, c42 = -54.0 / 125.0, c43 = -2.0 / 5.0, b1 = 19.0 / 9.0, b2 = 1.0 / 2.0,
@@ -672,14 +685,14 @@ __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx,
                  gamma = 1.0 / 2.0, c1X = 1.0 / 2.0, c2X = -3.0 / 2.0, c3X = 121.0 / 50.0, c4X = 29.0 / 250.0;
     const int t = g.tid, N = cx->nEqn;
     double *Y0 = VEC(0), *Y = VEC(1), *D0 = VEC(2), *DX = VEC(3), *K1 = VEC(4), *K2 = VEC(5), *K3 = VEC(6), *K4 = VEC(7), *DY = VEC(8);
-    const int st = lu_factor(cx, base, 1.0 / (gamma * dx));
+    const int st = lu_factor<DAC>(cx, base, 1.0 / (gamma * dx));
     if (st) { cs.fail = st; return 0.0; }
     if (t == 0) CNT(CNT_JAC)++;    // algorithmic count: the reference evaluates the Jacobian in every attempt
 #pragma unroll 1
     for (int s = 0; s < 4; ++s) {
         if (s == 1 || s == 2) {
             if (t < N) Y[t] = (s == 1) ? Y0[t] + a21 * K1[t] : Y0[t] + a31 * K1[t] + a32 * K2[t];
-            derivatives(cx, base, Y, DY);
+            derivatives<DAC>(cx, base, Y, DY);
         }
         double* K = VEC(4 + s);
         if (t < N) {
@@ -690,7 +703,7 @@ __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx,
             else r = DY[t] + dx * c4X * DX[t] + (c41 * K1[t] + c42 * K2[t] + c43 * K3[t]) / dx;
             K[t] = r;
         }
-        lu_solve(cx, base, K);
+        lu_solve<DAC>(cx, base, K);
     }
     double em = 0.0;
     if (t < N) {
@@ -703,16 +716,17 @@ __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx,
 }
 
 // adaptiveSolver::solve (A.3)
+template <bool DAC>
 __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, double& dxTry) {
     const double safeScale = 0.9, alphaInc = 0.2, alphaDec = 0.25, minScale = 0.2, maxScale = 10;
     const int t = g.tid, N = cx->nEqn;
     double dx = dxTry, err = 0.0;
     // dydx0 and the Jacobian are both evaluated at (y0, T0)
-    jacobian(cx, base, VEC(0), VEC(3), VEC(2));
+    jacobian<DAC>(cx, base, VEC(0), VEC(3), VEC(2));
     if (t == 0) CNT(CNT_JAC)--;                 // counted per attempt in rosenbrock34_step
     do {
         if (t == 0) CNT(CNT_ATTEMPTS)++;
-        err = rosenbrock34_step(g, cx, base, cs, dx);
+        err = rosenbrock34_step<DAC>(g, cx, base, cs, dx);
         if (cs.fail) return;
         if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
         if (err > 1) {
@@ -734,12 +748,13 @@ __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, doub
 // seulex::seul (A.5): one extrapolation column; y0 = V4, scale = V5, result in V6.
 // `phase` keeps derivatives() and lu_solve() at one call site each: phase 1 = the stability check of the
 // second sub-step (solves dyc), phase 0 = the regular Euler increment (solves dy).
+template <bool DAC>
 __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k) {
     const int t = g.tid, N = cx->nEqn;
     const int nSteps = c_nSeq[k];
     const double dx = dxTot / nSteps;
     double *y0 = VEC(4), *scale = VEC(5), *yOut = VEC(6), *dy = VEC(7), *yT = VEC(1), *f = VEC(8), *dyc = VEC(2);
-    const int st = lu_factor(cx, base, 1 / dx);
+    const int st = lu_factor<DAC>(cx, base, 1 / dx);
     if (st) { cs.fail = st; return false; }
     bool ok = true;
     int it = 0, phase = 0;
@@ -755,7 +770,7 @@ __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, 
                 if (t < N) f[t] = VEC(3)[t];
                 if (t == 0) CNT(CNT_RHS)++;
             } else {
-                derivatives(cx, base, it == 0 ? y0 : yT, f);
+                derivatives<DAC>(cx, base, it == 0 ? y0 : yT, f);
                 if (it == 0) { if (t < N) VEC(3)[t] = f[t]; cs.f0valid = 1; }
             }
             if (it == 1 && k <= 1) phase = 1;
@@ -770,7 +785,7 @@ __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, 
             if (t < N) dy[t] = f[t];
             rhs = dy;
         }
-        lu_solve(cx, base, rhs);
+        lu_solve<DAC>(cx, base, rhs);
         if (phase == 1) {
             const double denom = fmin(1.0, dy1 + LB_SMALL);
             double s2 = 0.0; int big = 0;
@@ -801,6 +816,7 @@ __device__ __forceinline__ double seulex_coeff(int k, int l) {
 }
 
 // seulex::solve (A.5); y = V0
+template <bool DAC>
 __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, StepState& step, int& attempts) {
     const int t = g.tid, N = cx->nEqn;
     const DevOpts& O = cx->O;
@@ -828,7 +844,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
     bool jacUpdated = false;
     if (cs.theta > jacRedo) {
         // the Jacobian's first rate sweep is at (y0, T0): it also yields f(y0) for the first Euler sub-step of every column
-        jacobian(cx, base, y, VEC(8), VEC(3));
+        jacobian<DAC>(cx, base, y, VEC(8), VEC(3));
         if (t == 0) CNT(CNT_RHS)--;            // counted when seul() consumes it
         cs.f0valid = 1;
         jacUpdated = true;
@@ -847,7 +863,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
         double errOld = 0;
 #pragma unroll 1
         for (k = 0; k <= cs.kTarg + 1; ++k) {
-            const bool success = seul(g, cx, base, cs, dx, k);
+            const bool success = seul<DAC>(g, cx, base, cs, dx, k);
             if (cs.fail) return;
             if (!success) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
             double s = 0.0;
@@ -866,7 +882,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
                 }
             }
             if (k != 0) {
-                const double err = sqrt(g.sum(s, 1) / cs.nOde);
+                const double err = sqrt(g.sum(s, 1) / CNT(CNT_NODE));
                 if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
                 if (err > 1 / LB_SMALL || (k > 1 && err >= errOld)) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
                 errOld = fmin(4 * err, 1.0);
@@ -914,7 +930,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
             step.prevReject = 1;
             if (!jacUpdated) {
                 cs.theta = 2.0 * jacRedo;
-                if (cs.theta > jacRedo && !jacUpdated) { jacobian(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
+                if (cs.theta > jacRedo && !jacUpdated) { jacobian<DAC>(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
             }
         }
     }
@@ -947,7 +963,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
 }
 
 // ODESolver::solve (A.2); y = V0
-template <int SOLVER>
+template <int SOLVER, bool DAC>
 __device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double xStart, double xEnd, double& dxTry) {
     StepState step = {1, 1, 0, 0, 0, dxTry, 0.0};
     double x = xStart;
@@ -961,10 +977,10 @@ __device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* b
             step.dxTry = xEnd - x;
         }
         if (SOLVER == LBCHEM_SOLVER_SEULEX) {
-            seulex_solve(g, cx, base, cs, x, step, attempts);
+            seulex_solve<DAC>(g, cx, base, cs, x, step, attempts);
         } else {
             const double x0 = x;
-            adaptive_solve(g, cx, base, cs, x, step.dxTry);
+            adaptive_solve<DAC>(g, cx, base, cs, x, step.dxTry);
             step.dxDid = x - x0;
         }
         if (cs.fail) return;
@@ -985,7 +1001,7 @@ __device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* b
 constexpr int CTX_BYTES = 512;
 static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
 
-template <int SOLVER>
+template <int SOLVER, bool DAC>
 __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
     extern __shared__ double smem[];
     unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
@@ -1025,7 +1041,8 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
         double dtChem = B.deltaTChem[cell];
         if (t < CNT_N) CNT(t) = 0;
-        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0; cs.nOde = cx->nEqn;
+        Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0;
+        if (t == 0) CNT(CNT_NODE) = cx->nEqn;
         int status;
         double Tend = T0;
         double* y = VEC(0);
@@ -1034,16 +1051,15 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
             if (t == nSp) y[nSp] = T0;
             if (t == nSp + 1) y[nSp + 1] = p0;
             g.sync();
-            if (cx->dac) {
+            if (DAC) {
                 // LoadBalancedTDAC solveCell with mechRed()->active() (reference LoadBalancedTDACChemistryModel.C:385-393)
                 const int ns = dac_reduce(cx, base, y);
-                if (t == 0 && B.nActive) B.nActive[cell] = ns;
-                cs.nOde = ns + 2;
+                if (t == 0) { CNT(CNT_NODE) = ns + 2; if (B.nActive) B.nActive[cell] = ns; }
             }
             double timeLeft = deltaT;
             while (timeLeft > LB_SMALL) {
                 double dt = timeLeft;
-                ode_solve<SOLVER>(g, cx, base, cs, 0.0, dt, dtChem);
+                ode_solve<SOLVER, DAC>(g, cx, base, cs, 0.0, dt, dtChem);
                 g.sync();
                 if (t < nSp) y[t] = fmax(0.0, y[t]);
                 g.sync();
@@ -1057,7 +1073,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
             }
             // the reduced call of the reference passes cData.T() for both T and p (:406-409): the aliased reference ends up
             // holding the p slot, i.e. the temperature the cell came in with
-            Tend = cx->dac ? T0 : y[nSp];
+            Tend = DAC ? T0 : y[nSp];
             status = cs.fail ? cs.fail : LBCHEM_CELL_OK;
         } else {
             if (t < nSp) B.RR[(size_t)t * B.ldy + cell] = 0.0;
@@ -1098,18 +1114,30 @@ int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol) {
 bool lb_v3_supported(const V2Mech& M) { return M.nEqn <= v3::TPC && M.nEqn >= 3; }
 int lb_v3_ctx_bytes() { return v3::CTX_BYTES; }
 
+template <int SOLVER, bool DAC>
+static cudaError_t v3_attr(size_t smemBytes) {
+    return cudaFuncSetAttribute(v3::integrate_v3_kernel<SOLVER, DAC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+}
+
+// both variants of the solver's kernel: full mechanism, and DAC-reduced (selected per launch by M.dac)
 cudaError_t lb_v3_configure(int solver, size_t smemBytes) {
-    return solver == LBCHEM_SOLVER_SEULEX
-               ? cudaFuncSetAttribute(v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes)
-               : cudaFuncSetAttribute(v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    cudaError_t e = solver == LBCHEM_SOLVER_SEULEX ? v3_attr<LBCHEM_SOLVER_SEULEX, false>(smemBytes)
+                                                   : v3_attr<LBCHEM_SOLVER_ROSENBROCK34, false>(smemBytes);
+    if (e != cudaSuccess) return e;
+    return solver == LBCHEM_SOLVER_SEULEX ? v3_attr<LBCHEM_SOLVER_SEULEX, true>(smemBytes)
+                                          : v3_attr<LBCHEM_SOLVER_ROSENBROCK34, true>(smemBytes);
 }
 
 cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s) {
-    if (solver == LBCHEM_SOLVER_SEULEX)
-        v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX><<<grid, groups * v3::TPC, smemBytes, s>>>(M, O, B, wsDoubles);
-    else
-        v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34><<<grid, groups * v3::TPC, smemBytes, s>>>(M, O, B, wsDoubles);
+    const int block = groups * v3::TPC;
+    if (solver == LBCHEM_SOLVER_SEULEX) {
+        if (M.dac) v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX, true><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+        else v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+    } else {
+        if (M.dac) v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, true><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+        else v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+    }
     return cudaGetLastError();
 }
 
