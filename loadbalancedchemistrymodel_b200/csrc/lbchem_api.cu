@@ -465,7 +465,7 @@ int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int3
         V2Mech probe = h->V2;
         lb_v3_workspace(probe, LBCHEM_SOLVER_ROSENBROCK34, 1e-2, 1e-12);
         const int cap = std::max(h->V2.nSp * (h->V2.nSp + 1), 2 * h->V2.nR);
-        if (h->dacPairs > cap) return fail(h, LBCHEM_E_UNSUPPORTED, "reduction: species-pair table does not fit the per-cell workspace");
+        if (h->dacPairs + (h->dacPairs + 7) / 8 > cap) return fail(h, LBCHEM_E_UNSUPPORTED, "reduction: species-pair table does not fit the per-cell workspace");
     }
     h->dacProg[7] = n_init;
     for (int i = 0; i < 8; ++i) h->dacProg[8 + i] = i < n_init ? init_species[i] : 0;

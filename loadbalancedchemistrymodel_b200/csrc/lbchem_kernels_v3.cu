@@ -571,34 +571,53 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
     reaction_sweep<true>(cx, base, 0, T, lnT, invT);
     const double* OM = WS(OM);
     double* NUM = WS(A);
+    unsigned char* NB = reinterpret_cast<unsigned char*>(NUM + D[0]);     // neighbour B of each pair, after the numerators
     double *PA = VEC(1), *CA = VEC(2), *RV = VEC(3);
-    const int* pairPtr = D + D[1];
-    if (t < nSp) {
-        const int* termPtr = D + D[2]; const unsigned* term = reinterpret_cast<const unsigned*>(D + D[3]);
-        const int* pcPtr = D + D[4]; const unsigned* pc = reinterpret_cast<const unsigned*>(D + D[5]);
-        int e = pairPtr[t];
+    int* pairPtr = reinterpret_cast<int*>(VEC(5));
+    constexpr int PF = 8;                                                  // program words fetched ahead (L2 round trips)
+    {
+        // pair numerators: thread t owns a contiguous run of pairs, balanced by term count
+        const unsigned* term = reinterpret_cast<const unsigned*>(D + D[3]);
+        const int k0 = (D + D[2])[t], k1 = (D + D[2])[t + 1];
+        int e = (D + D[6])[t];
         double acc = 0.0;
-        const int k1 = termPtr[t + 1];
 #pragma unroll 1
-        for (int k = termPtr[t]; k < k1; ++k) {
-            const unsigned w = term[k];
-            acc = __dadd_rn(acc, __dmul_rn((double)(int)(signed char)(w >> 16), OM[w & 0xffffu]));
-            if ((w >> 24) & 1u) { NUM[e++] = acc; acc = 0.0; }
+        for (int k = k0; k < k1; k += PF) {
+            unsigned w[PF];
+#pragma unroll
+            for (int q = 0; q < PF; ++q) w[q] = term[k + q];               // padded by PF words on the host
+#pragma unroll
+            for (int q = 0; q < PF; ++q) {
+                if (k + q < k1) {
+                    acc = __dadd_rn(acc, __dmul_rn((double)(int)(signed char)(w[q] >> 16), OM[w[q] & 0xffffu]));
+                    if ((w[q] >> 24) & 1u) { NUM[e] = acc; NB[e] = (unsigned char)((w[q] >> 25) & 63u); ++e; acc = 0.0; }
+                }
+            }
         }
+    }
+    if (t <= nSp) pairPtr[t] = (D + D[1])[t];
+    if (t < nSp) {
+        const int* pcPtr = D + D[4]; const unsigned* pc = reinterpret_cast<const unsigned*>(D + D[5]);
         double pa = 0.0, ca = 0.0;
         const int q1 = pcPtr[t + 1];
 #pragma unroll 1
-        for (int k = pcPtr[t]; k < q1; ++k) {
-            const unsigned w = pc[k];
-            const double wA = __dmul_rn((double)(int)(signed char)(w >> 16), OM[w & 0xffffu]);
-            if (wA > 0.0) pa += wA; else ca += -wA;
+        for (int k = pcPtr[t]; k < q1; k += PF) {
+            unsigned w[PF];
+#pragma unroll
+            for (int q = 0; q < PF; ++q) w[q] = pc[k + q];
+#pragma unroll
+            for (int q = 0; q < PF; ++q) {
+                if (k + q < q1) {
+                    const double wA = __dmul_rn((double)(int)(signed char)(w[q] >> 16), OM[w[q] & 0xffffu]);
+                    if (wA > 0.0) pa += wA; else ca += -wA;
+                }
+            }
         }
         PA[t] = pa; CA[t] = ca; RV[t] = 0.0;
     }
     g.sync();
     if (g.warp == 0) {
         unsigned char* Q = reinterpret_cast<unsigned char*>(VEC(4));
-        const unsigned char* nb = reinterpret_cast<const unsigned char*>(D + D[6]);
         const double tol = __hiloint2double(D[17], D[16]);
         unsigned long long act = 0ull;
         int head = 0, tail = 0;
@@ -624,7 +643,7 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
                     const int v = v0 + g.lane;
                     bool cond = false; int Bsp = 0; double Rt = 0.0;
                     if (v < n) {
-                        Bsp = nb[e0 + v];
+                        Bsp = NB[e0 + v];
                         double r = fabs(NUM[e0 + v]) / Den;
                         if (r > 1.0) r = 1.0;
                         Rt = Ru * r;

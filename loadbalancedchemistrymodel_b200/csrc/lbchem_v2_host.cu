@@ -56,11 +56,13 @@ static void reaction_order(const lbchem_mech_desc* m, std::vector<int>& order, s
 
 // DAC program (chemistryReductionMethods::DAC::reduceMechanism; reference call site LoadBalancedTDACChemistryModel.C:388).
 // One int array, offsets in ints from its start:
-//   [0] nPairs  [1] pairPtr  [2] termPtr  [3] term  [4] pcPtr  [5] pc  [6] nb (bytes)  [7] nInit  [8..15] initial set
-//   [16],[17] tolerance (lo, hi words)
+//   [0] nPairs  [1] pairPtr[nSp+1]  [2] thrTerm[65]  [3] term  [4] pcPtr[nSp+1]  [5] pc  [6] thrPair[65]  [7] nInit
+//   [8..15] initial set  [16],[17] tolerance (lo, hi words)
 // pairPtr[A]..pairPtr[A+1]: the (A,B) pairs of species A in first-appearance order of B (the rABPos order);
-// term: per species the contributions net_nu_A(reaction) * omega[pos] to its pair numerators, pair by pair, reactions
-// ascending (bit 24 closes a pair); pc: per species the net_nu_A * omega[pos] of every reaction holding A (P_A / C_A).
+// term: the contributions net_nu_A(reaction) * omega[pos] to the pair numerators, pair by pair, reactions ascending
+// (bits 0-15 pos, 16-23 signed net nu, bit 24 closes a pair, bits 25-30 B); thread t of a cell owns the pairs
+// [thrPair[t], thrPair[t+1]) = terms [thrTerm[t], thrTerm[t+1]); pc: per species the net_nu_A * omega[pos] of every
+// reaction holding A (P_A / C_A).
 int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut) {
     const int nSp = m->n_species, nR = m->n_reactions;
     if (nSp > 64 || nInit < 1 || nInit > 8 || !(tol > 0.0)) return 1;
@@ -96,32 +98,45 @@ int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32
             pcOf[A].push_back({posOf[r], net[a]});
         }
     }
-    std::vector<int> pairPtr(nSp + 1, 0), termPtr(nSp + 1, 0), pcPtr(nSp + 1, 0);
-    std::vector<unsigned> term, pc; std::vector<unsigned char> nb;
+    std::vector<int> pairPtr(nSp + 1, 0), pcPtr(nSp + 1, 0), pairTerms;
+    std::vector<unsigned> term, pc;
     for (int A = 0; A < nSp; ++A) {
         for (int Bsp : nbOf[A]) {
             const auto& L = termsOf[A][Bsp];
             for (size_t q = 0; q < L.size(); ++q)
-                term.push_back((unsigned)L[q].pos | ((unsigned)(uint8_t)(int8_t)L[q].coef << 16) | ((q + 1 == L.size()) ? 1u << 24 : 0u));
-            nb.push_back((unsigned char)Bsp);
+                term.push_back((unsigned)L[q].pos | ((unsigned)(uint8_t)(int8_t)L[q].coef << 16) | ((q + 1 == L.size()) ? 1u << 24 : 0u) |
+                               ((unsigned)Bsp << 25));
+            pairTerms.push_back((int)L.size());
         }
         for (const auto& c : pcOf[A]) pc.push_back((unsigned)c.pos | ((unsigned)(uint8_t)(int8_t)c.coef << 16));
-        pairPtr[A + 1] = (int)nb.size(); termPtr[A + 1] = (int)term.size(); pcPtr[A + 1] = (int)pc.size();
+        pairPtr[A + 1] = (int)pairTerms.size(); pcPtr[A + 1] = (int)pc.size();
     }
-    while (nb.size() % 4) nb.push_back(0);
+    // deal the pairs to the 64 threads of a cell in contiguous runs balanced by term count (a pair is never split)
+    const int nPairs = (int)pairTerms.size();
+    std::vector<int> thrPair(V2_TPC + 1, nPairs), thrTerm(V2_TPC + 1, (int)term.size());
+    {
+        const double total = (double)term.size();
+        double acc = 0; int th = 0, tsum = 0;
+        thrPair[0] = 0; thrTerm[0] = 0;
+        for (int e = 0; e < nPairs; ++e) {
+            while (th + 1 < V2_TPC && acc >= total * (th + 1) / V2_TPC) { ++th; thrPair[th] = e; thrTerm[th] = tsum; }
+            acc += pairTerms[e]; tsum += pairTerms[e];
+        }
+        while (th + 1 <= V2_TPC) { ++th; thrPair[th] = nPairs; thrTerm[th] = tsum; }
+    }
     prog.assign(18, 0);
-    prog[0] = pairPtr[nSp];
+    prog[0] = nPairs;
     auto put = [&](int slot, const void* src, size_t bytes) {
         prog[slot] = (int)prog.size();
         const int* s = static_cast<const int*>(src);
         prog.insert(prog.end(), s, s + bytes / 4);
     };
-    put(1, pairPtr.data(), pairPtr.size() * 4); put(2, termPtr.data(), termPtr.size() * 4);
     if (term.empty()) term.push_back(0);
     if (pc.empty()) pc.push_back(0);
-    if (nb.empty()) nb.resize(4, 0);
+    for (int q = 0; q < 8; ++q) { term.push_back(0); pc.push_back(0); }      // the kernel reads eight words ahead
+    put(1, pairPtr.data(), pairPtr.size() * 4); put(2, thrTerm.data(), thrTerm.size() * 4);
     put(3, term.data(), term.size() * 4); put(4, pcPtr.data(), pcPtr.size() * 4); put(5, pc.data(), pc.size() * 4);
-    put(6, nb.data(), nb.size());
+    put(6, thrPair.data(), thrPair.size() * 4);
     prog[7] = nInit;
     for (int i = 0; i < nInit; ++i) { if (init[i] < 0 || init[i] >= nSp) return 1; prog[8 + i] = init[i]; }
     std::memcpy(&prog[16], &tol, 8);
