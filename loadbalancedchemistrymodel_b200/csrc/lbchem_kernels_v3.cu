@@ -455,8 +455,10 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     bool done = (t >= nSp) || !((act >> t) & 1ull);
     int pos = t;
     if (done && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
+    int par = 1;      // exchange buffer, toggled per pivot column (with DAC two consecutive pivot columns may share j & 1)
 #pragma unroll 1
     for (int j = DAC ? next_col(act, 0, nSp) : 0; j < nSp; j = DAC ? next_col(act, j + 1, nSp) : j + 1) {
+        par ^= 1;
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
         const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
@@ -467,7 +469,6 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
         const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
         const bool win = c2 && pp == mp;
-        const int par = j & 1;
         if (win) {
             double* slot = XCH + (g.warp * 2 + par) * 4;
             slot[0] = __longlong_as_double((long long)key);
