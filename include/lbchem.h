@@ -190,6 +190,14 @@ int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy,
 int lbchem_get_stats(lbchem_handle h, lbchem_stats* out);
 
 /*
+ * Heat release rate Qdot[c] = -sum_i hf_i RR_i[c]  [W/m3], hf_i = formation enthalpy per mass of species i
+ * (OpenFOAM StandardChemistryModel::Qdot(), which the combustion model calls right after solve(); the reference inherits
+ * it unchanged, LoadBalancedChemistryModel.H:58-60). DEVICE pointers, stream-ordered; RR as written by
+ * lbchem_solve_batch ([nSp][ldy]).
+ */
+int lbchem_qdot(lbchem_handle h, int64_t n, int64_t ldy, const double* RR, double* Qdot, void* stream);
+
+/*
  * Test hook: evaluate one building block of the integrator for nItems states on the device, with the
  * same device functions lbchem_solve_batch uses (so a parity failure can be localised). HOST pointers;
  * strides in doubles. With n = n_species + 2 and y = (c[0..nSp), T, p):

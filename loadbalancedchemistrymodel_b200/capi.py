@@ -140,6 +140,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
     lib.lbchem_set_reduction.argtypes = [H, C.c_int32, C.c_double, C.c_int32, _ip]
     lib.lbchem_get_active_species.argtypes = [H, C.c_int64, _ip]
+    lib.lbchem_qdot.argtypes = [H, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.lbchem_probe.argtypes = [H, C.c_int32, C.c_int32, _dp, C.c_int32, _dp, C.c_int32]
     lib.lbchem_fp64_peak.argtypes = [C.c_int, C.c_double, _dp, _dp]
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
@@ -153,7 +154,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species"
+    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot"
 ).split()
 
 
@@ -282,6 +283,12 @@ class Chemistry:
                                          ptr(deltaTChem), ptr(RR), ptr(Tout), ptr(cost), ptr(status),
                                          C.c_void_p(int(stream)))
         self._check(rc, "lbchem_solve_batch")
+
+    def qdot_device(self, n, ldy, RR, Qdot, stream=0):
+        """Qdot [W/m3] from the RR block of the last solve (torch CUDA tensors or anything with data_ptr())."""
+        rc = self.lib.lbchem_qdot(self.h, int(n), int(ldy), C.c_void_p(RR.data_ptr()), C.c_void_p(Qdot.data_ptr()),
+                                  C.c_void_p(int(stream)))
+        self._check(rc, "lbchem_qdot")
 
     def probe(self, kind, x):
         """x [nItems, inStride] -> out [nItems, outStride] (see include/lbchem.h: lbchem_probe)."""

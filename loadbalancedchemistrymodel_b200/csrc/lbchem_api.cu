@@ -16,6 +16,7 @@
 
 int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err);
 int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
+cudaError_t lb_launch_qdot(long long n, long long ldy, int nSp, const double* hf, const double* RR, double* Qdot, cudaStream_t s);
 int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut);
 bool lb_v2_supported_size(int nEqn);
 cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
@@ -78,6 +79,8 @@ struct lbchem_handle_t {
     // DAC reduction (LoadBalancedTDAC): host copy of the program, device copy, per-cell NsDAC_ of the last batch
     std::vector<int> dacProg; int dacPairs = 0; int* dDac = nullptr; bool dacOn = false;
     int* dNActive = nullptr; long long nActiveCap = 0, nActiveOff = 0;
+    // Qdot: dimensionless formation enthalpies ha_low(Tstd)/R per species (host), hf = RR/W * that in J/kg (device)
+    std::vector<double> hfOverR, Wsp; double* dHf = nullptr; double hfGas = -1;
     int v2Groups = 0; size_t v2Smem = 0;
     double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
     void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
@@ -392,6 +395,12 @@ int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) 
     if (rc != LBCHEM_OK) return rc;
     {
         std::string e;
+        h->hfOverR.resize(mech->n_species); h->Wsp.assign(mech->W, mech->W + mech->n_species);
+        for (int i = 0; i < mech->n_species; ++i) {
+            // janafThermo::hc(): the low-range enthalpy polynomial at Tstd = 298.15 K
+            const double* a = mech->janaf_low + 7 * i; const double Ts = 298.15;
+            h->hfOverR[i] = ((((a[4] / 5.0 * Ts + a[3] / 4.0) * Ts + a[2] / 3.0) * Ts + a[1] / 2.0) * Ts + a[0]) * Ts + a[5];
+        }
         {
             const int32_t seed = 0;
             if (lb_dac_program(mech, 1e-4, 1, &seed, h->dacProg, &h->dacPairs) != 0) h->dacProg.clear();
@@ -418,6 +427,7 @@ int lbchem_destroy(lbchem_handle h) {
     if (h->dStats) cudaFree(h->dStats);
     if (h->dScratch) cudaFree(h->dScratch);
     if (h->dDac) cudaFree(h->dDac);
+    if (h->dHf) cudaFree(h->dHf);
     if (h->dNActive) cudaFree(h->dNActive);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
@@ -475,6 +485,21 @@ int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int3
     CK(cudaMemcpy(h->dDac, h->dacProg.data(), h->dacProg.size() * sizeof(int), cudaMemcpyHostToDevice));
     h->V2.dac = h->dDac;
     h->dacOn = true;
+    return LBCHEM_OK;
+}
+
+int lbchem_qdot(lbchem_handle h, int64_t n, int64_t ldy, const double* RR, double* Qdot, void* stream) {
+    if (!h || n < 0 || ldy < n || (n > 0 && (!RR || !Qdot))) return h ? fail(h, LBCHEM_E_INVALID, "bad Qdot arguments") : LBCHEM_E_INVALID;
+    CK(cudaSetDevice(h->device));
+    const int nSp = h->M.nSp;
+    if (!h->dHf) CK(cudaMalloc(&h->dHf, sizeof(double) * nSp));
+    if (h->hfGas != h->opts.gas_constant) {
+        std::vector<double> hf(nSp);
+        for (int i = 0; i < nSp; ++i) hf[i] = h->opts.gas_constant / h->Wsp[i] * h->hfOverR[i];
+        CK(cudaMemcpy(h->dHf, hf.data(), sizeof(double) * nSp, cudaMemcpyHostToDevice));
+        h->hfGas = h->opts.gas_constant;
+    }
+    if (n > 0) CK(lb_launch_qdot(n, ldy, nSp, h->dHf, RR, Qdot, static_cast<cudaStream_t>(stream)));
     return LBCHEM_OK;
 }
 

@@ -43,3 +43,33 @@ extern "C" int lbchem_fp64_peak(int device, double ms_target, double* tflops, do
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
     return LBCHEM_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Qdot = -sum_i hf_i RR_i  [W/m3]  (OpenFOAM StandardChemistryModel::Qdot, called by the combustion model right after
+// solve()). HBM-bound: one thread per cell walks the field-major RR block, consecutive threads read
+// consecutive addresses of each species row; (nSp + 1) * 8 bytes per cell.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) qdot_kernel(long long n, long long ldy, int nSp, const double* __restrict__ hf,
+                                                   const double* __restrict__ RR, double* __restrict__ Qdot) {
+    for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < n; c += (long long)gridDim.x * blockDim.x) {
+        double q0 = 0.0, q1 = 0.0;
+        int i = 0;
+        for (; i + 1 < nSp; i += 2) {
+            q0 = fma(-hf[i], RR[(size_t)i * ldy + c], q0);
+            q1 = fma(-hf[i + 1], RR[(size_t)(i + 1) * ldy + c], q1);
+        }
+        if (i < nSp) q0 = fma(-hf[i], RR[(size_t)i * ldy + c], q0);
+        Qdot[c] = q0 + q1;
+    }
+}
+
+cudaError_t lb_launch_qdot(long long n, long long ldy, int nSp, const double* hf, const double* RR, double* Qdot, cudaStream_t s) {
+    int dev = 0, sms = 148;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)sms * 8;          // a multiple of the SM count; grid-stride beyond that
+    if (blocks > cap) blocks = cap;
+    qdot_kernel<<<(int)blocks, 256, 0, s>>>(n, ldy, nSp, hf, RR, Qdot);
+    return cudaGetLastError();
+}

@@ -253,3 +253,50 @@ def test_gri_flame_fixture_dac_parity(gri, flame, solver, rel_tol):
     ref_full = O.OracleModel(gri, opts).solve_batch(Y[:, :256], T[:256], p[:256], rho[:256], DT, DTCHEM, nthreads=8)
     _compare(gri, Y[:, :256], rho[:256], full, ref_full, DT, f"gri-dac-off/{solver}")
     chem.close()
+
+
+def test_qdot_kernel(gri, flame):
+    """lbchem_qdot against -sum_i hf_i RR_i in numpy (hf from the low janaf range at Tstd, janafThermo::hc), on the RR of
+    a fixture solve and on a 2 M-cell random block where its HBM throughput is printed (466 B per cell algorithmic)."""
+    import torch
+    sel = np.arange(0, flame["T"].shape[0], 4)
+    Y, T, p, rho = _state(gri, flame, sel)
+    opts = capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1)
+    chem = capi.Chemistry(gri, opts)
+    got = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+    Ts = 298.15
+    a = gri.janaf_low
+    hf = opts.gas_constant * (((((a[:, 4] / 5 * Ts + a[:, 3] / 4) * Ts + a[:, 2] / 3) * Ts + a[:, 1] / 2) * Ts + a[:, 0]) * Ts + a[:, 5]) / gri.W
+    want = -(hf[:, None] * got["RR"]).sum(0)
+    dev = torch.device("cuda:0")
+    RR = torch.from_numpy(got["RR"]).to(dev)
+    Q = torch.empty(sel.size, dtype=torch.float64, device=dev)
+    chem.qdot_device(sel.size, sel.size, RR, Q)
+    torch.cuda.synchronize()
+    q = Q.cpu().numpy()
+    assert np.allclose(q, want, rtol=1e-12, atol=1e-9 * np.abs(want).max())
+    # heat is released where the fixture's own Qdot field says so
+    strong = np.abs(flame["Qdot"][sel]) > 1e6
+    assert (np.sign(q[strong]) == np.sign(flame["Qdot"][sel][strong])).mean() > 0.98
+    # ragged leading dimension + empty batch
+    n, ldy = 1000, 1536
+    RRp = torch.randn((gri.n_species, ldy), dtype=torch.float64, device=dev)
+    Qp = torch.zeros(n, dtype=torch.float64, device=dev)
+    chem.qdot_device(n, ldy, RRp, Qp)
+    chem.qdot_device(0, ldy, RRp, Qp)
+    torch.cuda.synchronize()
+    assert np.allclose(Qp.cpu().numpy(), -(hf[:, None] * RRp[:, :n].cpu().numpy()).sum(0), rtol=1e-12, atol=1e-9)
+    # throughput on a block larger than L2
+    n = 2_000_000
+    RRb = torch.randn((gri.n_species, n), dtype=torch.float64, device=dev)
+    Qb = torch.empty(n, dtype=torch.float64, device=dev)
+    for _ in range(3):
+        chem.qdot_device(n, n, RRb, Qb)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(10):
+        chem.qdot_device(n, n, RRb, Qb)
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 10
+    print(f"qdot: {n} cells in {ms:.3f} ms = {(gri.n_species + 1) * 8 * n / ms / 1e6:.0f} GB/s")
+    chem.close()
