@@ -52,14 +52,18 @@ extern "C" int lbchem_fp64_peak(int device, double ms_target, double* tflops, do
 __global__ void __launch_bounds__(256) qdot_kernel(long long n, long long ldy, int nSp, const double* __restrict__ hf,
                                                    const double* __restrict__ RR, double* __restrict__ Qdot) {
     for (long long c = blockIdx.x * (long long)blockDim.x + threadIdx.x; c < n; c += (long long)gridDim.x * blockDim.x) {
-        double q0 = 0.0, q1 = 0.0;
+        double q0 = 0.0, q1 = 0.0, q2 = 0.0, q3 = 0.0;
         int i = 0;
-        for (; i + 1 < nSp; i += 2) {
-            q0 = fma(-hf[i], RR[(size_t)i * ldy + c], q0);
-            q1 = fma(-hf[i + 1], RR[(size_t)(i + 1) * ldy + c], q1);
+        // eight independent loads in flight per thread before the first FMA needs one
+        for (; i + 7 < nSp; i += 8) {
+            double r[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) r[u] = __ldcs(RR + (size_t)(i + u) * ldy + c);
+            q0 = fma(-hf[i], r[0], q0); q1 = fma(-hf[i + 1], r[1], q1); q2 = fma(-hf[i + 2], r[2], q2); q3 = fma(-hf[i + 3], r[3], q3);
+            q0 = fma(-hf[i + 4], r[4], q0); q1 = fma(-hf[i + 5], r[5], q1); q2 = fma(-hf[i + 6], r[6], q2); q3 = fma(-hf[i + 7], r[7], q3);
         }
-        if (i < nSp) q0 = fma(-hf[i], RR[(size_t)i * ldy + c], q0);
-        Qdot[c] = q0 + q1;
+        for (; i < nSp; ++i) q0 = fma(-hf[i], __ldcs(RR + (size_t)i * ldy + c), q0);
+        Qdot[c] = (q0 + q1) + (q2 + q3);
     }
 }
 
