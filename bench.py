@@ -61,7 +61,7 @@ def make_workload(name, n, rank, world=1):
     return W.gri_uniform(n, rank=rank)
 
 
-DAC_TOL, DAC_INIT = 1e-4, ("CO", "CH4", "HO2")   # reference tests/Cases/Case-chemistry/constant/chemistryProperties:46,52-57
+DAC_TOL, DAC_INIT = float(os.environ.get("LBCHEM_DAC_TOL", "1e-4")), ("CO", "CH4", "HO2")   # reference tests/Cases/Case-chemistry/constant/chemistryProperties:46,52-57
 
 
 def dac_initial_set(mech):
