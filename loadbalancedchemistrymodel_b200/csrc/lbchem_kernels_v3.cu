@@ -396,15 +396,29 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_JAC]++;
 }
 
-// DAC: columns of kept species only. First set bit of `act` at index >= j (nSp when none) / last set bit at index <= j (-1 when none)
-__device__ __forceinline__ int next_col(unsigned long long act, int j, int nSp) {
-    const unsigned long long r = act & (~0ull << j);
-    return r ? __ffsll((long long)r) - 1 : nSp;
-}
-__device__ __forceinline__ int prev_col(unsigned long long act, int j) {
-    const unsigned long long r = act & ((2ull << j) - 1ull);
-    return r ? 63 - __clzll((long long)r) : -1;
-}
+// DAC: walk the columns of the kept species only. The 64-bit active word is held as two 32-bit halves: taking the lowest
+// (highest) remaining bit is one FLO + one logic op, where 64-bit shifts and find-first-set cost a dozen instructions per
+// column (15 % of the reduced kernel's instructions in the first version).
+struct ColsUp {
+    unsigned lo, hi; int j, nSp;
+    __device__ __forceinline__ ColsUp(bool dac, unsigned long long act, int n) : lo((unsigned)act), hi((unsigned)(act >> 32)), j(-1), nSp(n) { (void)dac; }
+    template <bool DAC> __device__ __forceinline__ bool next() {
+        if (!DAC) return ++j < nSp;
+        if (lo) { j = __ffs((int)lo) - 1; lo &= lo - 1u; return true; }
+        if (hi) { j = 31 + __ffs((int)hi); hi &= hi - 1u; return true; }
+        return false;
+    }
+};
+struct ColsDown {
+    unsigned lo, hi; int j;
+    __device__ __forceinline__ ColsDown(unsigned long long act, int nSp) : lo((unsigned)act), hi((unsigned)(act >> 32)), j(nSp) {}
+    template <bool DAC> __device__ __forceinline__ bool next() {
+        if (!DAC) return --j >= 0;
+        if (hi) { const int b = 31 - __clz((int)hi); j = 32 + b; hi ^= 1u << b; return true; }
+        if (lo) { const int b = 31 - __clz((int)lo); j = b; lo ^= 1u << b; return true; }
+        return false;
+    }
+};
 
 // ------------------------------------------------------------------------------------------------
 // dense linear algebra on the shared-memory matrix: thread t owns species row t of  dg*I - J
@@ -457,7 +471,8 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     if (done && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
     int par = 1;      // exchange buffer, toggled per pivot column (with DAC two consecutive pivot columns may share j & 1)
 #pragma unroll 1
-    for (int j = DAC ? next_col(act, 0, nSp) : 0; j < nSp; j = DAC ? next_col(act, j + 1, nSp) : j + 1) {
+    for (ColsUp cu(DAC, act, nSp); cu.next<DAC>();) {
+        const int j = cu.j;
         par ^= 1;
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
@@ -529,7 +544,8 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     if (t < nSp && !sp) x[t] = bt * RD[t];          // removed species: decoupled diagonal row
     // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
-    for (int j = DAC ? next_col(act, 0, nSp) : 0; j < nSp; j = DAC ? next_col(act, j + 1, nSp) : j + 1) {
+    for (ColsUp cu(DAC, act, nSp); cu.next<DAC>();) {
+        const int j = cu.j;
         if (step == j) BS[j] = bt;
         g.sync();
         if (sp && step > j) bt = fma(-row[j], BS[j], bt);
@@ -540,7 +556,8 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     g.sync();
     if (sp) bt = fma(-row[nSp], BS[nSp], bt);
 #pragma unroll 1
-    for (int j = DAC ? prev_col(act, nSp - 1) : nSp - 1; j >= 0; j = DAC ? (j > 0 ? prev_col(act, j - 1) : -1) : j - 1) {
+    for (ColsDown cd(act, nSp); cd.next<DAC>();) {
+        const int j = cd.j;
         if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
         g.sync();
         if (sp && step < j) bt = fma(-row[j], BS[j], bt);
@@ -617,6 +634,19 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
         PA[t] = pa; CA[t] = ca; RV[t] = 0.0;
     }
     g.sync();
+    // r_AB = min(|num| / max(P_A, C_A), 1) for every pair of species A = t, ahead of the serial search (0 when the
+    // denominator is below VSMALL: the reference does not look at the neighbours of such a species)
+    if (t < nSp) {
+        const double Den = fmax(PA[t], CA[t]);
+        const int e1 = pairPtr[t + 1];
+#pragma unroll 2
+        for (int e = pairPtr[t]; e < e1; ++e) {
+            double r = fabs(NUM[e]) / Den;
+            if (r > 1.0) r = 1.0;
+            NUM[e] = (Den > LB_VSMALL) ? r : 0.0;
+        }
+    }
+    g.sync();
     if (g.warp == 0) {
         unsigned char* Q = reinterpret_cast<unsigned char*>(VEC(4));
         const double tol = __hiloint2double(D[17], D[16]);
@@ -635,8 +665,7 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
 #pragma unroll 1
         while (head < tail) {
             const int u = Q[head++];
-            const double Den = fmax(PA[u], CA[u]);
-            if (Den > LB_VSMALL) {
+            {
                 const int e0 = pairPtr[u], n = pairPtr[u + 1] - e0;
                 const double Ru = RV[u];
 #pragma unroll 1
@@ -645,9 +674,7 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
                     bool cond = false; int Bsp = 0; double Rt = 0.0;
                     if (v < n) {
                         Bsp = NB[e0 + v];
-                        double r = fabs(NUM[e0 + v]) / Den;
-                        if (r > 1.0) r = 1.0;
-                        Rt = Ru * r;
+                        Rt = Ru * NUM[e0 + v];
                         cond = Rt >= tol;
                     }
                     if (cond && Rt > RV[Bsp]) RV[Bsp] = Rt;
