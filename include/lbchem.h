@@ -198,6 +198,15 @@ int lbchem_get_stats(lbchem_handle h, lbchem_stats* out);
 int lbchem_qdot(lbchem_handle h, int64_t n, int64_t ldy, const double* RR, double* Qdot, void* stream);
 
 /*
+ * Chemical time scale tc[c] = nReaction * sum_i c_i / (SMALL + sum_r (sum_rhs nu) * forward rate of r)  [s]
+ * (OpenFOAM StandardChemistryModel::tc(), used by the EDC / PaSR combustion models next to solve(); inherited unchanged by
+ * the reference). DEVICE pointers, stream-ordered; same Y, T, p, rho arrays as lbchem_solve_batch. Needs a handle configured
+ * for seulex or Rosenbrock34 (it reuses that kernel's rate sweep).
+ */
+int lbchem_tc(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p, const double* rho,
+              double* tc, void* stream);
+
+/*
  * Test hook: evaluate one building block of the integrator for nItems states on the device, with the
  * same device functions lbchem_solve_batch uses (so a parity failure can be localised). HOST pointers;
  * strides in doubles. With n = n_species + 2 and y = (c[0..nSp), T, p):

@@ -141,6 +141,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_set_reduction.argtypes = [H, C.c_int32, C.c_double, C.c_int32, _ip]
     lib.lbchem_get_active_species.argtypes = [H, C.c_int64, _ip]
     lib.lbchem_qdot.argtypes = [H, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.lbchem_tc.argtypes = [H, C.c_int64, C.c_int64] + [C.c_void_p] * 6
     lib.lbchem_probe.argtypes = [H, C.c_int32, C.c_int32, _dp, C.c_int32, _dp, C.c_int32]
     lib.lbchem_fp64_peak.argtypes = [C.c_int, C.c_double, _dp, _dp]
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
@@ -154,7 +155,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot"
+    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc"
 ).split()
 
 
@@ -289,6 +290,12 @@ class Chemistry:
         rc = self.lib.lbchem_qdot(self.h, int(n), int(ldy), C.c_void_p(RR.data_ptr()), C.c_void_p(Qdot.data_ptr()),
                                   C.c_void_p(int(stream)))
         self._check(rc, "lbchem_qdot")
+
+    def tc_device(self, n, ldy, Y, T, p, rho, tc, stream=0):
+        """Chemical time scale [s] of every cell (torch CUDA tensors or anything with data_ptr())."""
+        ptr = lambda a: C.c_void_p(a.data_ptr())
+        rc = self.lib.lbchem_tc(self.h, int(n), int(ldy), ptr(Y), ptr(T), ptr(p), ptr(rho), ptr(tc), C.c_void_p(int(stream)))
+        self._check(rc, "lbchem_tc")
 
     def probe(self, kind, x):
         """x [nItems, inStride] -> out [nItems, outStride] (see include/lbchem.h: lbchem_probe)."""

@@ -16,6 +16,8 @@
 
 int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err);
 int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
+cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+                     double* tcOut, cudaStream_t s);
 cudaError_t lb_launch_qdot(long long n, long long ldy, int nSp, const double* hf, const double* RR, double* Qdot, cudaStream_t s);
 int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut);
 bool lb_v2_supported_size(int nEqn);
@@ -500,6 +502,24 @@ int lbchem_qdot(lbchem_handle h, int64_t n, int64_t ldy, const double* RR, doubl
         h->hfGas = h->opts.gas_constant;
     }
     if (n > 0) CK(lb_launch_qdot(n, ldy, nSp, h->dHf, RR, Qdot, static_cast<cudaStream_t>(stream)));
+    return LBCHEM_OK;
+}
+
+int lbchem_tc(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p, const double* rho,
+              double* tc, void* stream) {
+    if (!h) return LBCHEM_E_INVALID;
+    if (n < 0 || ldy < n || (n > 0 && (!Y || !T || !p || !rho || !tc))) return fail(h, LBCHEM_E_INVALID, "bad tc arguments");
+    CK(cudaSetDevice(h->device));
+    if (!h->useV3)
+        return fail(h, LBCHEM_E_UNSUPPORTED, "tc() runs on the compact-code kernel's rate sweep (solver seulex or Rosenbrock34, nEqn <= 64)");
+    if (n == 0) return LBCHEM_OK;
+    BatchArgs B{};
+    B.n = n; B.ldy = ldy; B.Y = Y; B.T = T; B.p = p; B.rho = rho;
+    B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
+    long long grid = h->nSM;
+    const long long need = (n + h->v3Groups - 1) / h->v3Groups;
+    if (grid > need) grid = need;
+    CK(lb_v3_tc((int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, tc, static_cast<cudaStream_t>(stream)));
     return LBCHEM_OK;
 }
 

@@ -1141,6 +1141,63 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// Chemical time scale of every cell (OpenFOAM StandardChemistryModel::tc()):
+//   tc = nReaction * sum_i c_i / (SMALL + sum_r (sum_rhs nu) * kf_r * prod_lhs c^e)
+// Same staging, workspace layout and rate sweep as the integration kernel; one cell per 64-thread group.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, double* tcOut) {
+    extern __shared__ double smem[];
+    unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
+    {
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(M.blob);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(sm + CTX_BYTES);
+        for (int i = threadIdx.x; i < M.hotBytes / 8; i += blockDim.x) dst[i] = src[i];
+    }
+    Ctx* cxw = reinterpret_cast<Ctx*>(sm);
+    if (threadIdx.x == 0) {
+        bind(cxw->S, M, sm + CTX_BYTES);
+        bind_cold(cxw->S, M);
+        cxw->O = O;
+        cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
+        cxw->wsDoubles = ctx_layout(*cxw, M);
+        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
+        cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
+    }
+    __syncthreads();
+    const Ctx* cx = cxw;
+    double* base = reinterpret_cast<double*>(sm + CTX_BYTES + M.hotBytes) + (size_t)(threadIdx.x / TPC) * wsDoubles;
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, nR = S.nR, t = g.tid;
+    const long long groups = (long long)gridDim.x * cx->groups;
+    for (long long cell = (long long)blockIdx.x * cx->groups + threadIdx.x / TPC; cell < B.n; cell += groups) {
+        g.sync();
+        double* y = VEC(0);
+        const double T = B.T[cell], rho = B.rho[cell];
+        double c = 0.0;
+        if (t < nSp) { c = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t]; y[t] = c; }
+        g.sync();
+        const double cSum = g.sum(c, 3);          // the reference sums the unclamped concentrations
+        const double lnT = log(T), invT = 1.0 / T;
+        prepare(g, cx, base, y, T, lnT, true);
+        reaction_sweep<false>(cx, base, 1, T, lnT, invT);
+        const double* KF = WS(A); const double* CC = WS(CC);
+        double s = 0.0;
+#pragma unroll 1
+        for (int p = t; p < nR; p += TPC) {
+            const unsigned iw = S.info[p];
+            const unsigned long long rp = S.rpk[p];
+            double nu = 0.0;
+            for (unsigned q = 0; q < V2_NR(iw); ++q) nu += (double)V2_NU(V2_SLOT(rp, q));
+            s = fma(nu, KF[p] * side_product(CC, S.lpk[p], V2_NL(iw)), s);
+        }
+        const double tot = g.sum(s, 3);
+        if (t == 0) tcOut[cell] = nR * cSum / (LB_SMALL + tot);
+    }
+}
+
 }  // namespace v3
 
 // ------------------------------------------------------------------------------------------------
@@ -1185,6 +1242,15 @@ cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int
         if (M.dac) v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, true><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
         else v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
     }
+    return cudaGetLastError();
+}
+
+cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+                     double* tcOut, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(v3::tc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (e != cudaSuccess) return e;
+    V2Mech Mm = M; Mm.dac = nullptr;
+    v3::tc_v3_kernel<<<grid, groups * v3::TPC, smemBytes, s>>>(Mm, O, B, wsDoubles, tcOut);
     return cudaGetLastError();
 }
 

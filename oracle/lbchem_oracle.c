@@ -1283,6 +1283,24 @@ int oracle_solve_batch(const oracle_mech* M, const lbchem_options* opts, int seu
     return 0;
 }
 
+/* StandardChemistryModel::tc(): tc = nReaction * cSum / (SMALL + sum_r sum_rhs nu * pf * cf), c = rho Y / W unclamped */
+void oracle_tc(const oracle_mech* M, const lbchem_options* opts, int64_t n, int64_t ldy, const double* Y, const double* T,
+               const double* rho, double* tc) {
+    oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;
+    const lbchem_mech_desc* d = &M->d;
+    double c[M->nSp];
+    for (int64_t cell = 0; cell < n; ++cell) {
+        double cSum = 0, acc = O_SMALL;
+        for (int i = 0; i < M->nSp; ++i) { c[i] = rho[cell] * Y[i * ldy + cell] / d->W[i]; cSum += c[i]; }
+        for (int r = 0; r < M->nR; ++r) {
+            double pf, cf, pr, cr; int lRef, rRef;
+            omega_reaction(M, &O, r, c, T[cell], &pf, &cf, &lRef, &pr, &cr, &rRef);
+            for (int k = d->rhs_ptr[r]; k < d->rhs_ptr[r + 1]; ++k) acc += d->rhs_nu[k] * pf * cf;
+        }
+        tc[cell] = M->nR * cSum / acc;
+    }
+}
+
 /* probes used by the tests: RHS and Jacobian of one state (y = c[nSp], T, p) */
 void oracle_derivatives(const oracle_mech* M, const lbchem_options* opts, const double* y, double* dydt) {
     oracle_opts O; memset(&O, 0, sizeof(O)); O.o = *opts;

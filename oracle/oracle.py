@@ -50,6 +50,8 @@ def lib() -> C.CDLL:
         L.oracle_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
         L.oracle_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
         L.oracle_cells_to_send.restype = C.c_int32
+        L.oracle_tc.argtypes = [C.c_void_p, C.POINTER(Options), C.c_int64, C.c_int64, _dp, _dp, _dp, _dp]
+        L.oracle_tc.restype = None
         L.oracle_set_reduction.argtypes = [C.c_int, C.c_double, C.c_int, _ip, _ip]
         L.oracle_set_reduction.restype = None
         L.oracle_dac_reduce.argtypes = [C.c_void_p, C.POINTER(Options), C.c_double, C.c_int, _ip, _dp, C.c_double, _ip, _ip]
@@ -127,6 +129,14 @@ class OracleModel:
             _as_dp(rho), _as_dp(dT_arr), dT_u, _as_dp(dtc), _as_dp(RR), _as_dp(Tout), _as_dp(cpu), _as_dp(att),
             _as_ip(status), cnt, int(nthreads),
         )
+
+    def tc(self, Y, T, rho):
+        """Chemical time scale of every cell (StandardChemistryModel::tc)."""
+        Y = np.ascontiguousarray(Y, dtype=np.float64); T = np.ascontiguousarray(T, dtype=np.float64)
+        rho = np.ascontiguousarray(rho, dtype=np.float64)
+        out = np.zeros(T.size)
+        lib().oracle_tc(self.h, C.byref(self.options), T.size, T.size, _as_dp(Y), _as_dp(T), _as_dp(rho), _as_dp(out))
+        return out
 
     def derivatives(self, y):
         y = np.ascontiguousarray(y, dtype=np.float64)
