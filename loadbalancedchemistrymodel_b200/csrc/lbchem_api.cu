@@ -25,7 +25,6 @@ cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
 int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
 bool lb_v3_supported(const V2Mech& M);
 int lb_v3_ctx_bytes();
-void lb_v3_timing(unsigned long long out[8], bool reset);
 cudaError_t lb_v3_configure(int solver, size_t smemBytes);
 cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s);
@@ -692,12 +691,6 @@ int lbchem_get_stats(lbchem_handle h, lbchem_stats* out) {
     out->n_steps = st[0]; out->n_attempts = st[1]; out->n_jac = st[2]; out->n_lu = st[3]; out->n_solve = st[4];
     out->n_rhs = st[5]; out->n_failed = st[6]; out->n_cells = st[7];
     out->kernel_ms = ms; out->kernel_launches = h->launches;
-    if (getenv("LBCHEM_TIMING")) {      // debug builds with -DV3_TIMING only
-        unsigned long long tm[8]; lb_v3_timing(tm, true);
-        const double c = st[7] ? (double)st[7] : 1.0;
-        fprintf(stderr, "[v3 timing] cycles per cell: derivatives %.0f jacobian %.0f lu_factor %.0f lu_solve %.0f | LU: update(not-done) %.0f search %.0f barrier %.0f select %.0f  (calls per cell: rhs %.1f jac %.1f lu %.1f solve %.1f)\n",
-                tm[0] / c, tm[1] / c, tm[2] / c, tm[3] / c, tm[4] / c, tm[5] / c, tm[6] / c, tm[7] / c, st[5] / c, st[2] / c, st[3] / c, st[4] / c);
-    }
     return LBCHEM_OK;
 }
 

@@ -1254,5 +1254,3 @@ cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, cons
     return cudaGetLastError();
 }
 
-// debug hook kept for API compatibility (phase timing lives in the experimental 128-thread variant)
-void lb_v3_timing(unsigned long long out[8], bool reset) { (void)reset; for (int i = 0; i < 8; ++i) out[i] = 0; }

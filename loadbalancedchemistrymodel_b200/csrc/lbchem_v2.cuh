@@ -43,8 +43,6 @@ struct V2Mech {
     const int* jthrEnt;                  // [65] first entry of thread t
     const int* jthrN;                    // [64] number of terms of thread t
     int jMaxTerms;
-    // the same program dealt to 128 threads (v3 kernel)
-    const unsigned long long* jterm3; const int* jthrEnt3; const int* jthrN3;
     const int* dac;                      // DAC program (lb_dac_program) when reduction is active, else null (v3 kernel)
     int tbRows;                          // rows of the seulex extrapolation table held per cell
     int wsDoubles;                       // per-cell workspace in doubles

@@ -344,7 +344,7 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         P.jterm = jterm; P.thrEnt = thrEnt; P.thrN = thrN; P.maxT = maxT;
         return P;
     };
-    Prog P64 = deal(V2_TPC), P128 = deal(128);
+    Prog P64 = deal(V2_TPC);
     M.jMaxTerms = P64.maxT;
     M.blobBytes = (int)B.b.size();
     auto up = [&](const void* src, size_t bytes, const void** dst) -> bool {
@@ -355,11 +355,9 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         *dst = d;
         return true;
     };
-    const void *dBlob, *dTerm, *dEnt, *dN, *dTerm3, *dEnt3, *dN3;
+    const void *dBlob, *dTerm, *dEnt, *dN;
     if (!up(B.b.data(), B.b.size(), &dBlob) || !up(P64.jterm.data(), P64.jterm.size() * 8, &dTerm) ||
-        !up(P64.thrEnt.data(), P64.thrEnt.size() * 4, &dEnt) || !up(P64.thrN.data(), P64.thrN.size() * 4, &dN) ||
-        !up(P128.jterm.data(), P128.jterm.size() * 8, &dTerm3) || !up(P128.thrEnt.data(), P128.thrEnt.size() * 4, &dEnt3) ||
-        !up(P128.thrN.data(), P128.thrN.size() * 4, &dN3)) {
+        !up(P64.thrEnt.data(), P64.thrEnt.size() * 4, &dEnt) || !up(P64.thrN.data(), P64.thrN.size() * 4, &dN)) {
         err = "cudaMalloc/cudaMemcpy failed while uploading the packed mechanism";
         return LBCHEM_E_CUDA;
     }
@@ -367,9 +365,6 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     M.jterm = static_cast<const unsigned long long*>(dTerm);
     M.jthrEnt = static_cast<const int*>(dEnt);
     M.jthrN = static_cast<const int*>(dN);
-    M.jterm3 = static_cast<const unsigned long long*>(dTerm3);
-    M.jthrEnt3 = static_cast<const int*>(dEnt3);
-    M.jthrN3 = static_cast<const int*>(dN3);
     *out = M;
     return 0;
 }
