@@ -45,12 +45,14 @@ __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned c
 #undef P
 }
 
-// cp coefficients and the matrix sparsity lists are read once per call by a few threads: they stay in global memory
-// (L2-resident) so that the shared-memory copy of the mechanism is smaller and one more cell fits per SM.
+// cp coefficients and the matrix sparsity lists are read once per call by a few threads, the entropy polynomials once per
+// prepare() as one batch of independent coalesced loads: they stay in global memory (L2-resident) so that the
+// shared-memory copy of the mechanism is smaller and six cells fit per SM with an odd (conflict-free) matrix stride.
 __device__ __forceinline__ void bind_cold(SMech& S, const V2Mech& M) {
     if (M.hotBytes >= M.blobBytes) return;
 #define PC(T, off) reinterpret_cast<const T*>(M.blob + M.off)
     S.cpLo = PC(double, oCpLo); S.cpHi = PC(double, oCpHi); S.rowPtr = PC(int, oRowPtr); S.entCol = PC(unsigned char, oEntCol);
+    S.sLo = PC(double, oSLo); S.sHi = PC(double, oSHi);
 #undef PC
 }
 
@@ -128,7 +130,7 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oRD = p; p += N;
     c.oBS = p; p += N; c.oPIV = p; p += (N + 1) / 2;
     c.oSTEP = p; p += (N + 1) / 2;
-    c.lda = M.nSp + 1;                        // even for GRI (54): column accesses across rows are 2-way conflicted, rows are not
+    c.lda = (M.nSp + 1) | 1;                  // odd (GRI: 55): one column read across the 16 rows of a half-warp touches 16 distinct 8-byte banks
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
     return (p + 1) & ~1;
 }

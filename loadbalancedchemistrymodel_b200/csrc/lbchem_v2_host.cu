@@ -210,11 +210,9 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     {
         const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
         const int haI[6] = {4, 3, 2, 1, 0, 5}; const double haD[6] = {5, 4, 3, 2, 1, 1};
-        const int sI[6] = {4, 3, 2, 1, 0, 6};  const double sD[6] = {4, 3, 2, 1, 1, 1};
         M.oW = B.add(std::vector<double>(m->W, m->W + nSp));
         M.oTc = B.add(std::vector<double>(m->Tcommon, m->Tcommon + nSp));
         M.oHaLo = B.add(soa2(m->janaf_low, nSp, haI, haD, 6)); M.oHaHi = B.add(soa2(m->janaf_high, nSp, haI, haD, 6));
-        M.oSLo = B.add(soa2(m->janaf_low, nSp, sI, sD, 6));    M.oSHi = B.add(soa2(m->janaf_high, nSp, sI, sD, 6));
     }
     M.oA = B.add(A); M.oBeta = B.add(beta); M.oTa = B.add(Ta); M.oInfo = B.add(info);
     M.oLpk = B.add(lpk); M.oRpk = B.add(rpk);
@@ -295,11 +293,13 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         }
         while (row < N) rowPtr[++row] = (int)entCol.size();
     }
-    // cold tail of the blob (the v3 kernel leaves it in global memory): cp polynomials, matrix sparsity lists
+    // cold tail of the blob (the v3 kernel leaves it in global memory): cp and entropy polynomials, matrix sparsity lists
     M.hotBytes = (int)B.b.size();
     {
         const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
+        const int sI[6] = {4, 3, 2, 1, 0, 6};  const double sD[6] = {4, 3, 2, 1, 1, 1};
         M.oCpLo = B.add(soa2(m->janaf_low, nSp, cpI, cpD, 5)); M.oCpHi = B.add(soa2(m->janaf_high, nSp, cpI, cpD, 5));
+        M.oSLo = B.add(soa2(m->janaf_low, nSp, sI, sD, 6));    M.oSHi = B.add(soa2(m->janaf_high, nSp, sI, sD, 6));
     }
     M.oRowPtr = B.add(rowPtr);
     if (entCol.empty()) entCol.push_back(0);
