@@ -513,7 +513,18 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
             const double* __restrict__ prow = A + ptid * lda;
             double* __restrict__ mine = row;
             int k = j + 1;
-            // batches of four: all loads first, so the stores of one batch never wait behind its loads
+            // batches of eight, then four: all loads first, so the stores of one batch never wait behind its loads
+#pragma unroll 1
+            for (; k + 7 <= nSp; k += 8) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double p4 = prow[k + 4], p5 = prow[k + 5], p6 = prow[k + 6], p7 = prow[k + 7];
+                const double r0 = mine[k], r1 = mine[k + 1], r2 = mine[k + 2], r3 = mine[k + 3];
+                const double r4 = mine[k + 4], r5 = mine[k + 5], r6 = mine[k + 6], r7 = mine[k + 7];
+                mine[k] = fma(-l, p0, r0); mine[k + 1] = fma(-l, p1, r1);
+                mine[k + 2] = fma(-l, p2, r2); mine[k + 3] = fma(-l, p3, r3);
+                mine[k + 4] = fma(-l, p4, r4); mine[k + 5] = fma(-l, p5, r5);
+                mine[k + 6] = fma(-l, p6, r6); mine[k + 7] = fma(-l, p7, r7);
+            }
 #pragma unroll 1
             for (; k + 3 <= nSp; k += 4) {
                 const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
