@@ -47,6 +47,11 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=0, help="cells in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-imbalanced", action="store_true", help="skip the load-balancing record (north_star imbalanced batch)")
+    ap.add_argument("--no-extra-configs", action="store_true", help="N = 8: skip the BASELINE config 4 / 5 records")
+    ap.add_argument("--no-pageable", action="store_true")
+    ap.add_argument("--imbalanced-cells", type=int, default=1_000_000, help="cells in TOTAL of the imbalanced batch")
+    ap.add_argument("--imbalanced-steps", type=int, default=2)
     ap.add_argument("--carry-dtchem", action="store_true",
                     help="carry deltaTChem from step to step like the model does between flow steps (default for gri_skewed)")
     return ap.parse_args()
@@ -83,7 +88,7 @@ def config_dict(args, n_gpus, extra=None):
         "workload": f"{args.workload}: GRI-Mech 3.0 (53 species, 325 reactions), {args.cells} synthetic cells per GPU "
                     f"({WORKLOAD_TEXT[args.workload]})",
         "mechanism": "GRI-3.0", "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
-        "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; per step: all-gather of the cost, bit-exact plan, NCCL p2p forward/return of planned cells (model.py)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
+        "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; every step through lbchem_lb_solve (C++ driver: all-gather of the cost, bit-exact plan, device cellsToSend, NCCL p2p of field-major row slices, one two-segment launch)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
         "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
     }
     if args.carry_dtchem or args.workload == "gri_skewed":
@@ -174,6 +179,148 @@ class ClockSampler:
         return out
 
 
+def _events():
+    import torch
+    return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+
+class Ranks:
+    """torch.distributed plumbing of the bench: barrier, max / sum over ranks (device-timed numbers are max over ranks)."""
+
+    def __init__(self, world, dev):
+        self.world, self.dev = world, dev
+
+    def barrier(self):
+        import torch
+        import torch.distributed as dist
+        if self.world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(self, x, op="max"):
+        import torch
+        import torch.distributed as dist
+        t = torch.tensor([float(x)], dtype=torch.float64, device=self.dev)
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
+        return float(t.item())
+
+
+IMB = {"solver": "seulex", "absTol": 1e-12, "relTol": 1e-3, "deltaT": 1e-4}
+
+
+def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north_star"):
+    """The load-balancing experiment: `total_cells` in TOTAL (strong scaling), the hot 10 % contiguous at the start of the
+    global index space (rank 0 holds them), deltaTChem carried from step to step, integrated once without and once
+    with the redistribution (same lbchem_lb entry point, balance off / on). seulex 1e-12 / 1e-3 over deltaT = 1e-4 is the
+    calibration at which the hot 10 % hold 90 % of the sub-steps (oracle counters: 82.4 vs 1.0 attempts)."""
+    import torch
+    from loadbalancedchemistrymodel_b200 import capi
+    from loadbalancedchemistrymodel_b200 import workloads as W
+    from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel
+
+    world, dev = R.world, R.dev
+    n = total_cells // world
+    if dac:
+        mech, Y, T, p, rho = W.gri_tiled(n, rank=rank)
+        solver, atol, rtol, dT = "seulex", 1e-12, 1e-1, W.DELTA_T
+    else:
+        mech, Y, T, p, rho = W.gri_skewed(n, rank=rank, world=world)
+        solver, atol, rtol, dT = IMB["solver"], IMB["absTol"], IMB["relTol"], IMB["deltaT"]
+    nSp = mech.n_species
+    opts = capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol, cost_model=1)
+    chem = capi.Chemistry(mech, opts, device=local)
+    if dac:
+        chem.set_reduction(DAC_TOL, dac_initial_set(mech))
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+    hY, hT, hp, hrho = pin(Y), pin(T), pin(p), pin(rho)
+    dY, dT_, dp, drho = (t.to(dev) for t in (hY, hT, hp, hrho))
+    dtc0 = torch.full((n,), W.DELTA_T_CHEM0, dtype=torch.float64, device=dev)
+    rec = {"label": label, "total_cells": n * world, "cells_per_gpu": n, "solver": solver, "absTol": atol, "relTol": rtol, "deltaT": dT,
+           "tdac": bool(dac), "cost_model": "work units 9 nLU + nSolve + 3 nRHS + 12 nJac (lbchem_options.cost_model = 1)",
+           "deltaTChem": "1e-07 on step 0 (the firstTime_ local step), then carried"}
+    results = {}
+    for mode in ("unbalanced", "balanced"):
+        model = LoadBalancedChemistryModel(chem, tdac=dac, balance=(mode == "balanced"))
+        out = {"RR": torch.empty((nSp, n), dtype=torch.float64, device=dev), "T": torch.empty(n, dtype=torch.float64, device=dev),
+               "cost": torch.empty(n, dtype=torch.float64, device=dev), "status": torch.empty(n, dtype=torch.int32, device=dev)}
+        dtc = dtc0
+        nwarm = 1 if mode == "unbalanced" else 2          # step 0 is local in both; the balanced model plans on step 1
+        times, moved, nbytes, kms = [], 0, 0, []
+        for it in range(nwarm + steps):
+            R.barrier()
+            e0, e1 = _events()
+            e0.record()
+            model.solve(dY, dT_, dp, drho, dT, dtc, out=out)
+            e1.record()
+            R.barrier()
+            if not dac:
+                dtc = model.deltaTChem                     # carried (LoadBalancedTDAC never writes it back, quirk D.2)
+            if it >= nwarm:
+                times.append(R.reduce(e0.elapsed_time(e1)))
+                moved, nbytes = model.last["sent_cells"], model.last["sent_bytes"]
+                kms.append(chem.stats()["kernel_ms"])
+        st = chem.stats()
+        results[mode] = dict(ms=float(np.mean(times)), RR=out["RR"].clone(), dtc=model.deltaTChem.clone(), cost=out["cost"].clone(),
+                             moved=moved, nbytes=nbytes, total_cost=model.total_cost, kernel_ms=float(np.mean(kms)), failed=int(st["n_failed"]),
+                             plan=list(model.send_plan))
+        if mode == "balanced":
+            # end to end through the load-balanced entry point: pinned HOST arrays, H2D + step + D2H inside the timing
+            ho = {"RR": pin(np.empty((nSp, n))).numpy(), "T": pin(np.empty(n)).numpy(), "cost": pin(np.empty(n)).numpy(),
+                  "status": pin(np.empty(n, np.int32)).numpy(), "deltaTChem": pin(np.empty(n)).numpy()}
+            hd = model.deltaTChem.cpu().numpy() if not dac else np.full(n, W.DELTA_T_CHEM0)
+            model.solve_host(hY.numpy(), hT.numpy(), hp.numpy(), hrho.numpy(), dT, hd, ho)
+            R.barrier()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                model.solve_host(hY.numpy(), hT.numpy(), hp.numpy(), hrho.numpy(), dT, hd, ho)
+                _ = float(ho["cost"].sum())
+            R.barrier()
+            results["e2e_s"] = R.reduce((time.perf_counter() - t0) / steps)
+        model.close()
+    ub, bl = results["unbalanced"], results["balanced"]
+    same = bool(torch.equal(ub["RR"], bl["RR"]) and torch.equal(ub["dtc"], bl["dtc"]) and torch.equal(ub["cost"], bl["cost"]))
+    same = R.reduce(0.0 if same else 1.0) == 0.0
+    loads = None
+    if world > 1:
+        import torch.distributed as dist
+        mine = torch.tensor([ub["total_cost"]], dtype=torch.float64, device=dev)
+        allc = torch.empty(world, dtype=torch.float64, device=dev)
+        dist.all_gather_into_tensor(allc, mine)
+        loads = allc.cpu().numpy()
+    else:
+        loads = np.array([ub["total_cost"]])
+    moved = R.reduce(bl["moved"], "sum"); nbytes = R.reduce(bl["nbytes"], "sum")
+    ideal_ms = ub["ms"] * loads.mean() / loads.max()      # ms per cost unit (slowest rank, unbalanced) x the even share
+    # measured split on a sample: attempts of hot and cold cells with the sub-step guess carried
+    split = None
+    if rank == 0 and not dac:
+        ns = 2000
+        mech2, Ys, Ts, ps, rhos = W.gri_skewed(2 * ns, hot_fraction=0.5, seed=77)
+        c2 = capi.Chemistry(mech2, capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol), device=local)
+        r1 = c2.solve_host(Ys, Ts, ps, rhos, dT, W.DELTA_T_CHEM0)
+        r2 = c2.solve_host(Ys, Ts, ps, rhos, dT, r1["deltaTChem"])
+        c2.close()
+        h, c = float(r2["cost"][:ns].mean()), float(r2["cost"][ns:].mean())
+        split = {"attempts_hot_cell": h, "attempts_cold_cell": c, "hot_10pct_share_of_attempts": 0.1 * h / (0.1 * h + 0.9 * c)}
+    rec.update({
+        "ms_per_step_unbalanced": ub["ms"], "ms_per_step_balanced": bl["ms"], "speedup_from_balancing": ub["ms"] / bl["ms"],
+        "cells_per_s_balanced": n * world / (bl["ms"] * 1e-3), "cells_per_s_unbalanced": n * world / (ub["ms"] * 1e-3),
+        "cells_moved": int(moved), "nvlink_bytes_per_step": int(nbytes),
+        "rank_cost_unbalanced": [float(x) for x in loads], "ideal_ms": ideal_ms, "efficiency_vs_ideal": ideal_ms / bl["ms"],
+        "ideal_definition": "ms_per_step_unbalanced x mean(rank cost) / max(rank cost): the slowest rank's time per cost unit x an even share",
+        "bit_identical_to_unbalanced": same, "failed_cells": int(R.reduce(ub["failed"] + bl["failed"], "sum")),
+        "rank0_kernel_ms_balanced": bl["kernel_ms"], "rank0_kernel_ms_unbalanced": ub["kernel_ms"],
+        "rank0_send_plan": [[int(t), float(f)] for t, f in bl["plan"]],
+        "e2e": {"value": n * world / results["e2e_s"], "unit": UNIT, "ms_per_step": results["e2e_s"] * 1e3,
+                "entry": "lbchem_lb_solve_host (pinned host arrays; H2D, plan, NVLink exchange, integrate, return, D2H)",
+                "h2d_bytes_per_step": (nSp + 4) * n * 8, "d2h_bytes_per_step": (nSp + 3) * n * 8 + n * 4},
+        "measured_split": split,
+    })
+    chem.close()
+    return rec
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -189,6 +336,7 @@ def run_b200(args):
     dev = torch.device("cuda", local)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+    R = Ranks(world, dev)
 
     s, atol, rtol = SOLVERS[args.solver]
     n = args.cells
@@ -199,72 +347,60 @@ def run_b200(args):
         chem.set_reduction(DAC_TOL, dac_initial_set(mech))
 
     def pinned(a):
-        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
-        return t
+        return torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
 
     hY, hT, hp, hrho = pinned(Y), pinned(T), pinned(p), pinned(rho)
     dY, dT_, dp, drho = (t.to(dev, non_blocking=True) for t in (hY, hT, hp, hrho))
     dtc0 = torch.full((n,), W.DELTA_T_CHEM0, dtype=torch.float64, device=dev)
     dtc = torch.empty_like(dtc0)
-    dRR = torch.empty((nSp, n), dtype=torch.float64, device=dev)
-    dTout = torch.empty(n, dtype=torch.float64, device=dev)
-    dcost = torch.empty(n, dtype=torch.float64, device=dev)
-    dstatus = torch.empty(n, dtype=torch.int32, device=dev)
-    gathered = torch.zeros(world, dtype=torch.float64, device=dev)
-    cells_per_rank = np.full(world, n, np.int32)
+    dout = {"RR": torch.empty((nSp, n), dtype=torch.float64, device=dev), "T": torch.empty(n, dtype=torch.float64, device=dev),
+            "cost": torch.empty(n, dtype=torch.float64, device=dev), "status": torch.empty(n, dtype=torch.int32, device=dev),
+            "deltaTChem": dtc}
     torch.cuda.synchronize()
     stream = torch.cuda.current_stream().cuda_stream
 
-    from loadbalancedchemistrymodel_b200.model import CudaCellSolver, LoadBalancedChemistryModel
-    cell_solver = CudaCellSolver(chem)
-    model = LoadBalancedChemistryModel(nSp, cell_solver, dev) if world > 1 else None
-    moved = {"sent": 0, "recv": 0}
+    from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel
+    # N > 1: every step goes through the library's load-balanced entry point (lbchem_lb_solve: C++ driver + NCCL)
+    model = LoadBalancedChemistryModel(chem, tdac=(args.workload == "gri_dac")) if world > 1 else None
+    moved = {"sent": 0, "recv": 0, "bytes": 0}
     carry = args.carry_dtchem or args.workload == "gri_skewed"   # reference .C:130,398,490: the sub-step guess persists
-    state = {"first": True}
+    state = {"first": True, "launches": 0}
 
     def step_device():
-        # one LoadBalancedChemistryModel::solve(deltaT). N = 1: one kernel over the shard. N > 1: the host driver
-        # (model.py) -- all-gather of the cost, bit-exact plan, cellsToSend scan, NCCL p2p forward trip, own tail then
-        # received cells, return trip, unpack (reference .C:453-704); the first call is its firstTime_ branch.
+        # one LoadBalancedChemistryModel::solve(deltaT). N = 1: one kernel over the shard. N > 1: lbchem_lb_solve --
+        # all-gather of the cost, bit-exact plan, cellsToSend on the device, NCCL p2p forward trip, own tail + received
+        # cells in one launch, return trip, cost total (reference .C:453-704); the first call is its firstTime_ branch.
+        if not carry or state["first"]:
+            dtc.copy_(dtc0)
+        state["first"] = False
         if model is None:
-            if not carry or state["first"]:
-                dtc.copy_(dtc0)
-            state["first"] = False
-            chem.solve_device(n, n, dY, dT_, dp, drho, W.DELTA_T, dtc, dRR, dTout, dcost, dstatus, stream=stream)
-            cell_solver.launches += 1
+            chem.solve_device(n, n, dY, dT_, dp, drho, W.DELTA_T, dtc, dout["RR"], dout["T"], dout["cost"], dout["status"], stream=stream)
+            state["launches"] += 1
         else:
-            model.solve(dY, dT_, dp, drho, W.DELTA_T, None if (carry and model.deltaTChem is not None) else dtc0)
-            moved["sent"] = model.last.get("sent_cells", 0); moved["recv"] = model.last.get("recv_cells", 0)
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+            model.solve(dY, dT_, dp, drho, W.DELTA_T, dtc, out=dout)
+            state["launches"] += 3                      # integration kernel + the two cost-vector kernels of the step
+            moved["sent"] = model.last["sent_cells"]; moved["recv"] = model.last["recv_cells"]; moved["bytes"] = model.last["sent_bytes"]
 
     for _ in range(max(args.warmup, 3)):
         step_device()
-    barrier()
-    launches0 = cell_solver.launches
+    R.barrier()
+    launches0 = state["launches"]
     sampler = ClockSampler(local) if rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kernel_ms = []
-    barrier()
+    e0, e1 = _events()
+    R.barrier()
     e0.record()
     for _ in range(args.steps):
         step_device()
     e1.record()
-    barrier()
-    ms = e0.elapsed_time(e1)
-    gpu_launches = cell_solver.launches - launches0
+    R.barrier()
+    ms = R.reduce(e0.elapsed_time(e1))
+    gpu_launches = state["launches"] - launches0
     st = chem.stats()                      # counters + CUDA-event duration of the last integration kernel
-    kernel_ms.append(st["kernel_ms"])
-    t = torch.tensor([ms], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    k_ms = float(st["kernel_ms"])
     ms_per_step = ms / args.steps
     value = n * world / (ms_per_step * 1e-3)
     n_failed = int(st["n_failed"])
+    ref_RR = dout["RR"].cpu().numpy() if not carry else None
 
     # ---- end to end: pinned host buffers through the C ABI (H2D, integrate, D2H inside the timed region)
     e2e = None
@@ -272,31 +408,55 @@ def run_b200(args):
         out = {"RR": pinned(np.empty((nSp, n))).numpy(), "T": pinned(np.empty(n)).numpy(), "cost": pinned(np.empty(n)).numpy(),
                "status": pinned(np.empty(n, np.int32)).numpy(), "deltaTChem": pinned(np.empty(n)).numpy()}
         args_h = (hY.numpy(), hT.numpy(), hp.numpy(), hrho.numpy(), W.DELTA_T, W.DELTA_T_CHEM0)
+
+        def step_host():
+            if model is None:
+                chem.solve_host(*args_h, out=out)
+            else:
+                model.solve_host(*args_h, out)
         for _ in range(2):
-            chem.solve_host(*args_h, out=out)
-        barrier()
+            step_host()
+        R.barrier()
         t0 = time.perf_counter()
         ke = args.steps
         for _ in range(ke):
-            r = chem.solve_host(*args_h, out=out)
-            _ = float(r["cost"].sum())            # the step's result read on the host
-        barrier()
-        el = (time.perf_counter() - t0) / ke
-        t = torch.tensor([el], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        el = float(t.item())
+            step_host()
+            _ = float(out["cost"].sum())            # the step's result read on the host
+        R.barrier()
+        el = R.reduce((time.perf_counter() - t0) / ke)
         h2d = (nSp + 4) * n * 8
         d2h = (nSp + 3) * n * 8 + n * 4
         e2e = {"value": n * world / el, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": el * 1e3, "timing": "host wall clock around lbchem_solve_batch_host (blocking), max over ranks"}
+               "ms_per_step": el * 1e3,
+               "entry": "lbchem_solve_batch_host (3-stream chunked pipeline)" if model is None else "lbchem_lb_solve_host (load-balanced entry point)",
+               "timing": "host wall clock around the blocking call, max over ranks"}
+        if ref_RR is not None:
+            # the chunks of the host path overlap on the device: their results must be those of the one-launch device path
+            e2e["rr_bit_identical_to_device_path"] = bool(np.array_equal(out["RR"], ref_RR))
+        if model is None and not args.no_pageable:
+            pg = {k: np.empty_like(v) for k, v in out.items()}
+            args_p = (np.array(Y), np.array(T), np.array(p), np.array(rho), W.DELTA_T, W.DELTA_T_CHEM0)
+            chem.solve_host(*args_p, out=pg)
+            t0 = time.perf_counter()
+            for _ in range(2):
+                chem.solve_host(*args_p, out=pg)
+            e2e["pageable_value"] = n / ((time.perf_counter() - t0) / 2)
     clocks = sampler.stop() if sampler else None
+
+    # ---- the load-balancing records (every N): the north_star batch, and at N = 8 BASELINE configs 4 and 5
+    imbalanced, extra = None, {}
+    if not args.no_imbalanced and args.workload == "gri_uniform":
+        if model is not None:
+            model.close(); model = None
+        imbalanced = run_imbalanced(R, rank, local, args.imbalanced_cells, steps=args.imbalanced_steps)
+        if world == 8 and not args.no_extra_configs:
+            extra["config4_gri_skewed_4M"] = run_imbalanced(R, rank, local, 4_000_000, steps=1, label="BASELINE config 4")
+            extra["config5_gri_dac_1M"] = run_imbalanced(R, rank, local, 1_000_000, dac=True, steps=3, label="BASELINE config 5")
 
     if rank == 0:
         # ---- roofline of the dominant (only) kernel: FP64 pipe; HBM figure beside it
-        model = W.flop_model(mech)
-        flops = W.algorithmic_flops(model, st)
-        k_ms = float(np.mean(kernel_ms))
+        fm = W.flop_model(mech)
+        flops = W.algorithmic_flops(fm, st)
         peak = capi.fp64_peak(local, 300.0)
         ach = flops / (k_ms * 1e-3) / 1e12
         peaks = {}
@@ -305,40 +465,46 @@ def run_b200(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        hbm_ach = 912.0 * n / (k_ms * 1e-3) / 1e9
-        traffic = None          # dram bytes per launch from the committed ncu --set full capture of this same configuration
+        hbm_ach = 912.0 * st["n_cells"] / (k_ms * 1e-3) / 1e9
+        traffic, traffic_src = None, None   # dram bytes per launch from the committed ncu --set full capture of this kernel
         try:
-            tr = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())
-            key = f"{args.solver}:{n}"
+            tr = json.loads((ROOT / "profiles" / "r02_traffic.json").read_text())
+            key = f"{args.workload}:{args.solver}:{n}"
             if key in tr:
-                traffic = tr[key]["dram_bytes"]
+                traffic, traffic_src = tr[key]["dram_bytes"], tr[key].get("source")
         except Exception:
             pass
         roofline = {
             "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
+            "traffic_source": traffic_src,
             "kernel": "v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)", "kernel_ms": k_ms,
             "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
-            "flops_per_cell": flops / n, "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts"
+            "flops_per_cell": flops / max(1, st["n_cells"]), "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts"
                           + (" at the FULL system size n = 55 (upper bound: the reduced systems are smaller)" if args.workload == "gri_dac" else ""),
             "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
                     "bytes_per_cell": 912, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
         }
         cpu = None
-        if not args.no_cpu_baseline and world >= 1:
+        if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             n_sample = args.cpu_sample or min(n, 600 * cores)
-            rate, dtc_s, _ = cpu_oracle_rate(args, n_sample, cores)
+            rate, dtc_s, _ = cpu_oracle_rate(args, n_sample, cores, steps=1, warmup=1)
             cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-                   "sample": f"{n_sample} cells of the same workload, one pass, {cores} threads ({dtc_s:.1f} s)"}
+                   "sample": f"{n_sample} cells of the same workload, second of two passes, {cores} threads ({dtc_s:.1f} s)"}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config_dict(args, world), "clocks": clocks, "e2e": e2e,
             "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu,
             "stats_last_step": {k: int(v) for k, v in st.items() if k.startswith("n_")}, "failed_cells": n_failed,
-            "balance_last_step": ({"rank0_sent_cells": moved["sent"], "rank0_recv_cells": moved["recv"]} if world > 1 else None),
+            "balance_last_step": ({"rank0_sent_cells": moved["sent"], "rank0_recv_cells": moved["recv"],
+                                   "note": "uniform cost: the plan is empty by construction; see `imbalanced` for the exchange"} if world > 1 else None),
+            "imbalanced": imbalanced,
         }
+        line.update(extra)
         _emit(json.dumps(line))
+    if model is not None:
+        model.close()
     chem.close()
     if world > 1:
         dist.destroy_process_group()

@@ -115,7 +115,12 @@ typedef struct lbchem_options {
     double gas_constant;          /* RR, J/(kmol K); default 8314.47 (OpenFOAM thermodynamicConstants) */
     double kc_floor;              /* kr = kf / max(Kc, kc_floor); default 1e-6 */
     int32_t threads_per_cell;     /* 0 = choose from mechanism size; else 32/64/128 */
-    int32_t sort_by_cost;         /* 1 = dispatch cells to the work queue in descending last-cost order */
+    int32_t sort_by_cost;         /* 1 = lbchem_solve_batch dispatches cells to the work queue in descending order of the
+                                     cost[] array as it holds on ENTRY (the previous flow step's per-cell cost) */
+    int32_t seulex_errold_max;    /* seulex: errOld = max(4 err, 1) [1, Numerical Recipes] or min(4 err, 1) [0, default]:
+                                     doubtful OpenFOAM detail, a switch on both the kernel and the oracle */
+    int32_t cost_model;           /* per-cell cost written to cost[]: 0 = attempted sub-steps; 1 = integer work units
+                                     9 nLU + nSolve + 3 nRHS + 12 nJac (what those building blocks cost on this kernel) */
 } lbchem_options;
 
 typedef struct lbchem_handle_t* lbchem_handle;
@@ -170,7 +175,8 @@ int lbchem_get_active_species(lbchem_handle h, int64_t n, int32_t* n_active);
  *   deltaTChem [n]       chemical sub-step guess, in/out (clipped to deltaTChemMax on return)
  *   RR       [nSp][ldy]  reaction rates kg/m3/s, out
  *   Tout     [n]         temperature after the step, out (may be NULL)
- *   cost     [n]         per-cell cost = attempted sub-steps of this integration, out (may be NULL)
+ *   cost     [n]         per-cell cost of this integration (lbchem_options.cost_model), out (may be NULL); with
+ *                        sort_by_cost it is also read on entry (the previous step's cost, zeros on a first step)
  *   status   [n]         LBCHEM_CELL_*, out (may be NULL)
  * Returns LBCHEM_OK or a negative error; cell-level failures are reported in status only.
  */
@@ -180,7 +186,11 @@ int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy,
                        double* deltaTChem, double* RR, double* Tout, double* cost,
                        int32_t* status, void* stream);
 
-/* Same call with HOST pointers: stages through the handle's pinned/device buffers (H2D, solve, D2H). */
+/* Same call with HOST pointers: the cells are cut into chunks that cycle through three streams (H2D, integrate, D2H),
+ * copied straight from / to the caller's arrays. With pinned (page-locked) caller arrays the copies of one chunk overlap
+ * the integration of its neighbours; with pageable arrays every copy blocks the host and the chunks run one after the
+ * other. sort_by_cost is ignored here. One call at a time per handle; so is lbchem_solve_batch (one batch in flight per
+ * handle: the work queue, the counters and the kernel scratch belong to the handle). */
 int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy,
                             const double* Y, const double* T, const double* p, const double* rho,
                             const double* deltaT, double deltaT_uniform,
@@ -207,17 +217,30 @@ int lbchem_tc(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const do
               double* tc, void* stream);
 
 /*
- * Test hook: evaluate one building block of the integrator for nItems states on the device, with the
- * same device functions lbchem_solve_batch uses (so a parity failure can be localised). HOST pointers;
- * strides in doubles. With n = n_species + 2 and y = (c[0..nSp), T, p):
- *   LBCHEM_PROBE_DERIV   in y[n]               out dydt[n]           StandardChemistryModel::derivatives
- *   LBCHEM_PROBE_JAC     in y[n]               out dfdx[n], J[n*n]   StandardChemistryModel::jacobian
- *   LBCHEM_PROBE_LUSOLVE in A[n*n], b[n]       out x[n]              LUDecompose + LUBacksubstitute
- *   LBCHEM_PROBE_RATES   in y[n]               out kf[nR], kr[nR]    Reaction::kf / kr
+ * Test hook: evaluate one building block of the integrator for nItems states on the device, with the device functions
+ * of the kernel the handle is configured to run (the compact-code kernel for seulex / Rosenbrock34 on mechanisms it
+ * supports, else the general kernel; threads_per_cell != 0 forces the general kernel), so that a parity failure can be
+ * localised. HOST pointers; strides in doubles. With n = n_species + 2 and y = (c[0..nSp), T, p):
+ *   LBCHEM_PROBE_DERIV       in y[n]               out dydt[n]           StandardChemistryModel::derivatives
+ *   LBCHEM_PROBE_JAC         in y[n]               out dfdx[n], J[n*n]   StandardChemistryModel::jacobian
+ *   LBCHEM_PROBE_LUSOLVE     in A[n*n], b[n]       out x[n]              LUDecompose + LUBacksubstitute (general kernel only)
+ *   LBCHEM_PROBE_RATES       in y[n]               out kf[nR], kr[nR]    Reaction::kf / kr
+ *   LBCHEM_PROBE_JAC_LUSOLVE in y[n], dg, b[n]     out x[n]              x = (dg I - J(y))^-1 b through jacobian +
+ *                                                                        LUDecompose + LUBacksubstitute as the ODE solvers
+ *                                                                        chain them (compact-code kernel only)
  */
-enum { LBCHEM_PROBE_DERIV = 0, LBCHEM_PROBE_JAC = 1, LBCHEM_PROBE_LUSOLVE = 2, LBCHEM_PROBE_RATES = 3 };
+enum { LBCHEM_PROBE_DERIV = 0, LBCHEM_PROBE_JAC = 1, LBCHEM_PROBE_LUSOLVE = 2, LBCHEM_PROBE_RATES = 3, LBCHEM_PROBE_JAC_LUSOLVE = 4 };
 int lbchem_probe(lbchem_handle h, int32_t kind, int32_t n_items, const double* in, int32_t in_stride,
                  double* out, int32_t out_stride);
+
+/*
+ * cellsToSend (LoadBalancedChemistryModel.C:143-167) on a DEVICE cost vector, nT targets in sequence: bounds[0] = 0,
+ * bounds[k+1] = first index >= bounds[k] at which the cost summed from bounds[k] reaches targets[k], else n.
+ * targets / bounds are HOST arrays. Bit-identical to lbchem_cells_to_send when the costs are integers (what the
+ * kernel writes). This is what lbchem_lb_solve runs; exported for tests.
+ */
+int lbchem_cells_to_send_device(lbchem_handle h, const double* cell_cost, int64_t n, const double* targets, int32_t nT,
+                                int64_t* bounds, void* stream);
 
 /*
  * FP64-pipe peak of the device (DFMA micro-benchmark, ~ms_target milliseconds): the roofline denominator of
@@ -241,6 +264,87 @@ int lbchem_balance_plan(int32_t nranks, const double* cost, const int32_t* cells
 
 /* cellsToSend: first index `end` >= start with sum(cost[start..end)) >= target, else n. Host pointers. */
 int32_t lbchem_cells_to_send(const double* cell_cost, int32_t n, double target, int32_t start);
+
+/* ------------------------------------------------------------------------------------------------------------------
+ * The load-balanced flow step: LoadBalancedChemistryModel::solve<DeltaTType>
+ *   reference src/chemistryModel/LoadBalancedChemistryModel/LoadBalancedChemistryModel.C:453-704
+ *   (first step local :471-509, plan :515-519 -> :170-347, cellsToSend + ship the first cells :521-570, own tail then
+ *    received cells :608-611, results returned in the same order :613-673, unpack + total cost :676-701)
+ *   and LoadBalancedTDACChemistryModel::solve<DeltaTType> (LoadBalancedTDACChemistryModel.C:623-979) with `tdac` set,
+ *   with src/pointToPointBuffer/pointToPointBuffer.C:53-168 replaced by NCCL point-to-point over NVLink (or a transport
+ *   the caller supplies). One lbchem_lb per rank (= per GPU, per host thread), on top of that rank's lbchem_handle.
+ * ------------------------------------------------------------------------------------------------------------------ */
+typedef struct lbchem_lb_t* lbchem_lb;
+
+typedef struct lbchem_lb_options {
+    int32_t update_iter;     /* LoadBalancedCoeffs{updateIter}: re-plan every update_iter + 1 steps (.C:41-45, 515-519) */
+    int32_t tdac;            /* 1 = LoadBalancedTDAC driver: absolute cost targets (TDAC .C:232,256), literal 2 % threshold
+                                (:214), deltaTChem[] is read but never written back (:968-971) */
+    double min_fraction;     /* LoadBalancedCoeffs{minFractionOfCellsToSend}, default 0.02 */
+    int32_t balance;         /* 0 = never exchange (every step takes the local branch: the non-balanced model) */
+    int32_t reserved;
+} lbchem_lb_options;
+
+/* what the last lbchem_lb_solve did on this rank */
+typedef struct lbchem_lb_info {
+    int32_t rank, nranks;
+    int32_t planned;          /* the plan was recomputed in this step */
+    int32_t exchanged;        /* the step took the exchange branch (0: first step / one rank / balance off) */
+    int32_t reallocated;      /* the receive block had to grow in this step */
+    int32_t n_send_partners, n_recv_partners;
+    int32_t reserved;
+    int64_t n_cells;          /* this rank's cells */
+    int64_t sent_cells;       /* own cells integrated by other ranks */
+    int64_t recv_cells;       /* other ranks' cells integrated here */
+    int64_t sent_bytes, recv_bytes;   /* both trips */
+    double total_cost;        /* totalCpuTime_ after the step: sum of this rank's per-cell costs */
+} lbchem_lb_info;
+
+/* one message of a grouped point-to-point exchange (ptr: device memory for lbchem_lb_create_transport) */
+typedef struct lbchem_p2p_op { int32_t is_send; int32_t peer; void* ptr; int64_t bytes; } lbchem_p2p_op;
+
+/* Caller-supplied transport (e.g. MPI from the OpenFOAM side). all_gather: `count` doubles per rank, HOST buffers,
+ * blocking. exchange: nops messages; messages between one pair of ranks match in posting order; blocking; called with
+ * the step's stream drained, must return when every receive has landed. Both return 0 on success. */
+typedef struct lbchem_transport {
+    void* ctx;
+    int (*all_gather)(void* ctx, const double* send, double* recv, int32_t count);
+    int (*exchange)(void* ctx, int32_t nops, const lbchem_p2p_op* ops);
+} lbchem_transport;
+
+void lbchem_lb_default_options(lbchem_lb_options* o);
+/* 128-byte NCCL unique id, made on one rank and broadcast by the caller (MPI_Bcast / any side channel). */
+int lbchem_lb_nccl_unique_id(void* id128);
+/* NCCL over NVLink / NVSwitch: one communicator per lbchem_lb (libnccl.so.2 is loaded on first use). */
+int lbchem_lb_create_nccl(lbchem_handle h, const void* id128, int32_t rank, int32_t nranks, const lbchem_lb_options* o, lbchem_lb* out);
+int lbchem_lb_create_transport(lbchem_handle h, const lbchem_transport* t, int32_t rank, int32_t nranks, const lbchem_lb_options* o, lbchem_lb* out);
+/* nranks ranks inside ONE process, one host thread each (lbchem_lb_solve of every rank must be called concurrently):
+ * messages are device-to-device copies. handles[r] may sit on the same or on different GPUs. out[nranks]. */
+int lbchem_lb_create_loopback(int32_t nranks, const lbchem_handle* handles, const lbchem_lb_options* o, lbchem_lb* out);
+int lbchem_lb_set_options(lbchem_lb lb, const lbchem_lb_options* o);
+int lbchem_lb_destroy(lbchem_lb lb);
+const char* lbchem_lb_last_error(lbchem_lb lb);
+
+/*
+ * One flow step over this rank's n cells: the argument list of lbchem_solve_batch (DEVICE pointers, stream-ordered
+ * work, but the call itself blocks on two or three small read-backs: the cost total, cellsToSend bounds, message sizes)
+ * plus *deltaTMin = min_c deltaTChem[c] after the step (what solve() returns before its 2*deltaT clamp, .C:714-718).
+ * Collective over the ranks. Tout, cost, status may be NULL. deltaT: all ranks pass per-cell arrays or all pass NULL.
+ * With 2+ ranks the cells [0, sent) of this rank are integrated elsewhere and their results written into RR / deltaTChem /
+ * Tout / cost / status by the return trip, exactly as if they had been integrated here.
+ */
+int lbchem_lb_solve(lbchem_lb lb, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p, const double* rho,
+                    const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR, double* Tout, double* cost,
+                    int32_t* status, double* deltaTMin, void* stream);
+/* The same step with HOST arrays (H2D, lbchem_lb_solve, D2H): what the OpenFOAM adapter calls with its fields. */
+int lbchem_lb_solve_host(lbchem_lb lb, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p, const double* rho,
+                         const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR, double* Tout, double* cost,
+                         int32_t* status, double* deltaTMin);
+int lbchem_lb_get_info(lbchem_lb lb, lbchem_lb_info* out);
+/* The plan this rank holds (sendAndReceiveData_, .H:84-96) and the split of the last step. Capacity nranks each;
+ * send_amount = fraction of the rank's total cost (standard) or absolute cost (tdac); bounds[nsend + 1]. */
+int lbchem_lb_get_plan(lbchem_lb lb, int32_t* nsend, int32_t* send_to, double* send_amount, int64_t* bounds,
+                       int32_t* nrecv, int32_t* recv_from, int64_t* recv_sizes);
 
 #ifdef __cplusplus
 }

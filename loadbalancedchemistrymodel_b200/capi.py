@@ -45,6 +45,7 @@ class Options(C.Structure):
         ("Treact", C.c_double), ("deltaTChemMax", C.c_double), ("cTauChem", C.c_double),
         ("eq_rate_limiter", C.c_int32), ("dfdx_is_dcdt", C.c_int32), ("gas_constant", C.c_double),
         ("kc_floor", C.c_double), ("threads_per_cell", C.c_int32), ("sort_by_cost", C.c_int32),
+        ("seulex_errold_max", C.c_int32), ("cost_model", C.c_int32),
     ]
 
 
@@ -56,6 +57,31 @@ class Stats(C.Structure):
     ]
 
 
+class LbOptions(C.Structure):
+    """lbchem_lb_options: LoadBalancedCoeffs{updateIter; minFractionOfCellsToSend} + the TDAC driver switch."""
+    _fields_ = [("update_iter", C.c_int32), ("tdac", C.c_int32), ("min_fraction", C.c_double), ("balance", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
+class LbInfo(C.Structure):
+    _fields_ = [("rank", C.c_int32), ("nranks", C.c_int32), ("planned", C.c_int32), ("exchanged", C.c_int32),
+                ("reallocated", C.c_int32), ("n_send_partners", C.c_int32), ("n_recv_partners", C.c_int32),
+                ("reserved", C.c_int32), ("n_cells", C.c_int64), ("sent_cells", C.c_int64), ("recv_cells", C.c_int64),
+                ("sent_bytes", C.c_int64), ("recv_bytes", C.c_int64), ("total_cost", C.c_double)]
+
+
+class P2POp(C.Structure):
+    _fields_ = [("is_send", C.c_int32), ("peer", C.c_int32), ("ptr", C.c_void_p), ("bytes", C.c_int64)]
+
+
+ALL_GATHER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, _dp, _dp, C.c_int32)
+EXCHANGE_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(P2POp))
+
+
+class Transport(C.Structure):
+    _fields_ = [("ctx", C.c_void_p), ("all_gather", ALL_GATHER_FN), ("exchange", EXCHANGE_FN)]
+
+
 # OpenFOAM v2306 thermodynamic::RR = 1e3 * NA * k (etc/controlDict DimensionedConstants, SI set)
 RR_DEFAULT = 1e3 * (6.0221417930e23 * 1.3806504e-23)
 
@@ -65,7 +91,7 @@ def default_options(**kw) -> Options:
     o = Options(
         solver=SOLVER_ROSENBROCK34, max_steps=10000, abs_tol=1e-15, rel_tol=1e-4, Treact=0.0,
         deltaTChemMax=1e15, cTauChem=1.0, eq_rate_limiter=0, dfdx_is_dcdt=1, gas_constant=RR_DEFAULT,
-        kc_floor=1e-6, threads_per_cell=0, sort_by_cost=0,
+        kc_floor=1e-6, threads_per_cell=0, sort_by_cost=0, seulex_errold_max=0, cost_model=0,
     )
     for k, v in kw.items():
         if k == "solver" and isinstance(v, str):
@@ -147,15 +173,61 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_balance_plan.argtypes = [C.c_int32, _dp, _ip, C.c_double, C.c_int32, _ip, _ip, _dp, _ip, _ip]
     lib.lbchem_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
     lib.lbchem_cells_to_send.restype = C.c_int32
+    lib.lbchem_cells_to_send_device.argtypes = [H, C.c_void_p, C.c_int64, _dp, C.c_int32, C.POINTER(C.c_int64), C.c_void_p]
+    declare_lb(lib)
+    L = C.c_void_p
+    lib.lbchem_lb_nccl_unique_id.argtypes = [C.c_void_p]
+    lib.lbchem_lb_create_nccl.argtypes = [H, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(LbOptions), C.POINTER(L)]
+    lib.lbchem_lb_create_transport.argtypes = [H, C.POINTER(Transport), C.c_int32, C.c_int32, C.POINTER(LbOptions), C.POINTER(L)]
+    lib.lbchem_lb_create_loopback.argtypes = [C.c_int32, C.POINTER(H), C.POINTER(LbOptions), C.POINTER(L)]
+    lib.lbchem_lb_solve_host.argtypes = [L, C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [C.c_double] + [C.c_void_p] * 5 + [_dp]
     if path is None:
         _lib = lib
     return lib
 
 
+def declare_lb(lib):
+    """Prototypes of the lbchem_lb_* entry points shared by liblbchem.so and the CPU test build liblbchem_lbhost.so."""
+    L = C.c_void_p
+    lib.lbchem_lb_default_options.argtypes = [C.POINTER(LbOptions)]
+    lib.lbchem_lb_set_options.argtypes = [L, C.POINTER(LbOptions)]
+    lib.lbchem_lb_destroy.argtypes = [L]
+    lib.lbchem_lb_last_error.argtypes = [L]
+    lib.lbchem_lb_last_error.restype = C.c_char_p
+    lib.lbchem_lb_solve.argtypes = [L, C.c_int64, C.c_int64] + [C.c_void_p] * 5 + [C.c_double] + [C.c_void_p] * 5 + [_dp, C.c_void_p]
+    lib.lbchem_lb_get_info.argtypes = [L, C.POINTER(LbInfo)]
+    lib.lbchem_lb_get_plan.argtypes = [L, _ip, _ip, _dp, C.POINTER(C.c_int64), _ip, _ip, C.POINTER(C.c_int64)]
+
+
+LBHOST_PATH = _HERE / "csrc" / "liblbchem_lbhost.so"
+HOST_SOLVER_FN = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int64, C.c_int64, _dp, _dp, _dp, _dp, _dp, C.c_double, _dp, _dp, _dp, _dp, _ip)
+_lbhost = None
+
+
+def load_lbhost() -> C.CDLL:
+    """The CPU TEST build of the load-balanced step (same C++ step logic, host memory, stand-in cell solver)."""
+    global _lbhost
+    if _lbhost is None:
+        if not LBHOST_PATH.exists():
+            raise RuntimeError(f"{LBHOST_PATH} not found: run __graft_entry__.build()")
+        lib = C.CDLL(str(LBHOST_PATH))
+        declare_lb(lib)
+        lib.lbchem_lbhost_create.argtypes = [C.c_int32, HOST_SOLVER_FN, C.c_void_p, C.POINTER(Transport), C.c_int32, C.c_int32,
+                                             C.POINTER(LbOptions), C.POINTER(C.c_void_p)]
+        _lbhost = lib
+    return _lbhost
+
+
+def lb_options(update_iter=0, min_fraction=0.02, tdac=False, balance=True) -> LbOptions:
+    return LbOptions(update_iter=int(update_iter), tdac=int(bool(tdac)), min_fraction=float(min_fraction), balance=int(bool(balance)), reserved=0)
+
+
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc"
+    "lbchem_cells_to_send lbchem_cells_to_send_device lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc "
+    "lbchem_lb_default_options lbchem_lb_nccl_unique_id lbchem_lb_create_nccl lbchem_lb_create_transport lbchem_lb_create_loopback "
+    "lbchem_lb_set_options lbchem_lb_destroy lbchem_lb_last_error lbchem_lb_solve lbchem_lb_solve_host lbchem_lb_get_info lbchem_lb_get_plan"
 ).split()
 
 
@@ -182,7 +254,7 @@ def cells_to_send(cell_cost, target, start=0, lib=None) -> int:
     return int(lib.lbchem_cells_to_send(_as_dp(cell_cost), cell_cost.shape[0], float(target), int(start)))
 
 
-PROBE_DERIV, PROBE_JAC, PROBE_LUSOLVE, PROBE_RATES = 0, 1, 2, 3
+PROBE_DERIV, PROBE_JAC, PROBE_LUSOLVE, PROBE_RATES, PROBE_JAC_LUSOLVE = 0, 1, 2, 3, 4
 
 
 class Chemistry:
@@ -297,12 +369,21 @@ class Chemistry:
         rc = self.lib.lbchem_tc(self.h, int(n), int(ldy), ptr(Y), ptr(T), ptr(p), ptr(rho), ptr(tc), C.c_void_p(int(stream)))
         self._check(rc, "lbchem_tc")
 
+    def cells_to_send_device(self, cost, targets, stream=0):
+        """cellsToSend on a device cost vector (torch CUDA tensor) for a sequence of targets; returns the bounds list."""
+        t = np.ascontiguousarray(targets, dtype=np.float64)
+        b = np.zeros(t.size + 1, np.int64)
+        rc = self.lib.lbchem_cells_to_send_device(self.h, C.c_void_p(cost.data_ptr()), int(cost.shape[0]), _as_dp(t), int(t.size),
+                                                  b.ctypes.data_as(C.POINTER(C.c_int64)), C.c_void_p(int(stream)))
+        self._check(rc, "lbchem_cells_to_send_device")
+        return [int(x) for x in b]
+
     def probe(self, kind, x):
         """x [nItems, inStride] -> out [nItems, outStride] (see include/lbchem.h: lbchem_probe)."""
         x = np.ascontiguousarray(x, dtype=np.float64)
         n = self.mech.n_species + 2
         nR = self.mech.n_reactions
-        out_w = {PROBE_DERIV: n, PROBE_JAC: n + n * n, PROBE_LUSOLVE: n, PROBE_RATES: 2 * nR}[kind]
+        out_w = {PROBE_DERIV: n, PROBE_JAC: n + n * n, PROBE_LUSOLVE: n, PROBE_RATES: 2 * nR, PROBE_JAC_LUSOLVE: n}[kind]
         out = np.zeros((x.shape[0], out_w))
         self._check(self.lib.lbchem_probe(self.h, kind, x.shape[0], _as_dp(x), x.shape[1], _as_dp(out), out_w),
                     "lbchem_probe")

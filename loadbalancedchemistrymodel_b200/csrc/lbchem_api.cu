@@ -10,104 +10,16 @@
 #include <string>
 #include <vector>
 
-#include "../../include/lbchem.h"
-#include "lbchem_device.cuh"
-#include "lbchem_v2.cuh"
+#include "lbchem_internal.hpp"
 
-int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err);
-int lb_v2_workspace(V2Mech& M, int solver, double relTol, double absTol);
-cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
-                     double* tcOut, cudaStream_t s);
-cudaError_t lb_launch_qdot(long long n, long long ldy, int nSp, const double* hf, const double* RR, double* Qdot, cudaStream_t s);
-int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut);
-bool lb_v2_supported_size(int nEqn);
-cudaError_t lb_v2_configure(int nEqn, int solver, size_t smemBytes);
-int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
-bool lb_v3_supported(const V2Mech& M);
-int lb_v3_ctx_bytes();
-cudaError_t lb_v3_configure(int solver, size_t smemBytes);
-cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
-                         const BatchArgs& B, cudaStream_t s);
-cudaError_t lb_v2_launch(int nEqn, int solver, int grid, int groups, size_t smemBytes, const V2Mech& M, const DevOpts& O,
-                         const BatchArgs& B, cudaStream_t s);
-size_t lb_work_doubles(const DevMech& M, int solver);
-cudaError_t lb_configure(int tpc, int groups, size_t smemBytes, int* ctasPerSM);
-cudaError_t lb_launch_integrate(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const DevMech& M,
-                                const DevOpts& O, const BatchArgs& B, cudaStream_t s);
-cudaError_t lb_launch_probe(int tpc, int groups, size_t smemBytes, int wsDoubles, const DevMech& M, const DevOpts& O,
-                            int kind, int nItems, const double* in, double* out, int inStride, int outStride, cudaStream_t s);
-
-namespace {
-
-constexpr int kStreams = 3;
-
-struct HostMech {   // host copy of the flattened tables (kept for re-partitioning when threads_per_cell changes)
-    int nSp = 0, nR = 0, nEff = 0;
-    std::vector<int> nl, nr, lsp, rsp, dbase;
-    std::vector<double> lnu, rnu;
-    int nTerms = 0;
-};
-
-struct Slot {       // per-stream staging for the host-pointer entry point
-    cudaStream_t stream = nullptr;
-    cudaEvent_t k0 = nullptr, k1 = nullptr;
-    double *Y = nullptr, *RR = nullptr, *T = nullptr, *p = nullptr, *rho = nullptr, *dT = nullptr, *dtc = nullptr,
-           *Tout = nullptr, *cost = nullptr;
-    int* status = nullptr;
-    unsigned long long* queue = nullptr;
-    long long cap = 0;
-    bool used = false;
-};
-
-}  // namespace
-
-struct lbchem_handle_t {
-    int device = 0;
-    int nSM = 0;
-    size_t smemMax = 0;
-    DevMech M{};
-    DevOpts O{};
-    lbchem_options opts{};
-    HostMech H;
-    std::vector<void*> allocs;
-    int tpc = 64, groups = 1, ctasPerSM = 1;
-    size_t wsDoubles = 0, smemBytes = 0;
-    int configuredSolver = -1, configuredTpc = -1;
-    V2Mech V2{};                     // packed mechanism of the fast path
-    bool v2Built = false, useV2 = false, useV3 = false;
-    int v3Groups = 0, v3Ws = 0; size_t v3Smem = 0;
-    double* dScratch = nullptr; int scratchStride = 0; size_t scratchCap = 0;
-    // DAC reduction (LoadBalancedTDAC): host copy of the program, device copy, per-cell NsDAC_ of the last batch
-    std::vector<int> dacProg; int dacPairs = 0; int* dDac = nullptr; bool dacOn = false;
-    int* dNActive = nullptr; long long nActiveCap = 0, nActiveOff = 0;
-    // Qdot: dimensionless formation enthalpies ha_low(Tstd)/R per species (host), hf = RR/W * that in J/kg (device)
-    std::vector<double> hfOverR, Wsp; double* dHf = nullptr; double hfGas = -1;
-    int v2Groups = 0; size_t v2Smem = 0;
-    double v2RelTol = -1, v2AbsTol = -1; int v2Solver = -1;
-    void* dThr = nullptr;            // device copy of thrPtr for the configured tpc
-    unsigned long long* dQueue = nullptr;
-    unsigned long long* dStats = nullptr;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-    bool evValid = false, hostPath = false;
-    int launches = 0;
-    long long lastN = 0;
-    Slot slots[kStreams];
-    std::string err;
-};
-
-namespace {
-
-int fail(lbchem_handle h, int code, const std::string& msg) {
+int lb_fail(lbchem_handle h, int code, const std::string& msg) {
     if (h) h->err = msg;
     return code;
 }
 
-#define CK(call)                                                                                   \
-    do {                                                                                           \
-        cudaError_t e_ = (call);                                                                   \
-        if (e_ != cudaSuccess)                                                                     \
-            return fail(h, LBCHEM_E_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));     \
-    } while (0)
+namespace {
+
+inline int fail(lbchem_handle h, int code, const std::string& msg) { return lb_fail(h, code, msg); }
 
 template <class T>
 int upload(lbchem_handle h, const std::vector<T>& v, const T** out) {
@@ -273,9 +185,7 @@ int configure_v2(lbchem_handle h) {
     const lbchem_options& o = h->opts;
     if (!h->v2Built || o.threads_per_cell != 0 || getenv("LBCHEM_GENERAL_KERNEL")) return LBCHEM_OK;
     if (o.solver != LBCHEM_SOLVER_SEULEX && o.solver != LBCHEM_SOLVER_ROSENBROCK34) return LBCHEM_OK;
-    // kernel generation: v3 (compact code, shared-memory LU) unless LBCHEM_KERNEL=v2 asks for the register-LU kernel
-    const char* gen = getenv("LBCHEM_KERNEL");
-    if (!(gen && !strcmp(gen, "v2")) && lb_v3_supported(h->V2)) {
+    if (lb_v3_supported(h->V2)) {
         const int ws = lb_v3_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol);
         const size_t per3 = (size_t)ws * sizeof(double);
         const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.hotBytes;
@@ -300,15 +210,6 @@ int configure_v2(lbchem_handle h) {
             return LBCHEM_OK;
         }
     }
-    if (!lb_v2_supported_size(h->V2.nEqn)) return LBCHEM_OK;
-    const size_t per = (size_t)lb_v2_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol) * sizeof(double);
-    if ((size_t)h->V2.blobBytes + per > h->smemMax) return LBCHEM_OK;
-    int groups = (int)std::min<size_t>(6, (h->smemMax - h->V2.blobBytes) / per);
-    if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
-    h->v2Groups = groups;
-    h->v2Smem = (size_t)h->V2.blobBytes + per * groups;
-    CK(lb_v2_configure(h->V2.nEqn, o.solver, h->v2Smem));
-    h->useV2 = true;
     return LBCHEM_OK;
 }
 
@@ -348,6 +249,7 @@ void set_devopts(lbchem_handle h) {
     d.solver = o.solver; d.maxSteps = o.max_steps; d.absTol = o.abs_tol; d.relTol = o.rel_tol; d.Treact = o.Treact;
     d.deltaTChemMax = o.deltaTChemMax; d.cTauChem = o.cTauChem; d.eqRateLimiter = o.eq_rate_limiter;
     d.dfdxIsDcdt = o.dfdx_is_dcdt; d.RR = o.gas_constant; d.kcFloor = o.kc_floor;
+    d.seulexErrOldMax = o.seulex_errold_max;
 }
 
 }  // namespace
@@ -375,6 +277,8 @@ void lbchem_default_options(lbchem_options* o) {
     o->kc_floor = 1e-6;
     o->threads_per_cell = 0;
     o->sort_by_cost = 0;
+    o->seulex_errold_max = 0;
+    o->cost_model = 0;
 }
 
 int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) {
@@ -406,7 +310,7 @@ int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) 
             const int32_t seed = 0;
             if (lb_dac_program(mech, 1e-4, 1, &seed, h->dacProg, &h->dacPairs) != 0) h->dacProg.clear();
         }
-        const int r2 = lb_v2_build(mech, &h->V2, h->allocs, e);
+        const int r2 = lb_v2_build(mech, &h->V2, h->allocs, e, &h->v3PosOf);
         if (r2 < 0) return fail(h, r2, e);
         h->v2Built = (r2 == 0);
     }
@@ -430,10 +334,14 @@ int lbchem_destroy(lbchem_handle h) {
     if (h->dDac) cudaFree(h->dDac);
     if (h->dHf) cudaFree(h->dHf);
     if (h->dNActive) cudaFree(h->dNActive);
+    if (h->dOrder) cudaFree(h->dOrder);
+    if (h->dProbeIn) cudaFree(h->dProbeIn);
+    if (h->dProbeOut) cudaFree(h->dProbeOut);
+    if (h->dHist) cudaFree(h->dHist);
     if (h->ev0) cudaEventDestroy(h->ev0);
     if (h->ev1) cudaEventDestroy(h->ev1);
     for (Slot& s : h->slots) {
-        void* ptrs[] = {s.Y, s.RR, s.T, s.p, s.rho, s.dT, s.dtc, s.Tout, s.cost, s.status, s.queue};
+        void* ptrs[] = {s.Y, s.RR, s.T, s.p, s.rho, s.dT, s.dtc, s.Tout, s.cost, s.status, s.queue, s.scratch};
         for (void* p : ptrs) if (p) cudaFree(p);
         if (s.k0) cudaEventDestroy(s.k0);
         if (s.k1) cudaEventDestroy(s.k1);
@@ -513,7 +421,7 @@ int lbchem_tc(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const do
         return fail(h, LBCHEM_E_UNSUPPORTED, "tc() runs on the compact-code kernel's rate sweep (solver seulex or Rosenbrock34, nEqn <= 64)");
     if (n == 0) return LBCHEM_OK;
     BatchArgs B{};
-    B.n = n; B.ldy = ldy; B.Y = Y; B.T = T; B.p = p; B.rho = rho;
+    B.a.n = n; B.a.ldy = ldy; B.a.Y = Y; B.a.T = T; B.a.p = p; B.a.rho = rho;
     B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
     long long grid = h->nSM;
     const long long need = (n + h->v3Groups - 1) / h->v3Groups;
@@ -541,45 +449,72 @@ static int reserve_nactive(lbchem_handle h, long long n) {
     return LBCHEM_OK;
 }
 
-static int launch(lbchem_handle h, long long n, long long ldy, const double* Y, const double* T, const double* p,
-                  const double* rho, const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR,
-                  double* Tout, double* cost, int32_t* status, unsigned long long* queue, cudaStream_t s) {
-    BatchArgs B;
-    B.n = n; B.ldy = ldy; B.Y = Y; B.T = T; B.p = p; B.rho = rho; B.deltaT = deltaT; B.deltaTUniform = deltaT_uniform;
-    B.deltaTChem = deltaTChem; B.RR = RR; B.Tout = Tout; B.cost = cost; B.status = status; B.order = nullptr;
-    B.queue = queue; B.stats = h->dStats; B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
-    B.nActive = nullptr;
+}  // extern "C"
+
+int lb_launch_batch(lbchem_handle h, const CellSeg* a, const CellSeg* b, double deltaTUniform, const int* order,
+                    unsigned long long* queue, double* scratch, cudaStream_t s) {
+    BatchArgs B{};
+    B.a = *a;
+    if (b) B.b = *b;
+    const long long n = B.a.n + B.b.n;
+    B.deltaTUniform = deltaTUniform; B.order = order;
+    B.queue = queue; B.stats = h->dStats; B.scratch = scratch; B.scratchStride = h->scratchStride;
+    B.costModel = h->opts.cost_model;
+    if (n <= 0) return LBCHEM_OK;
     CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
-    if (h->dacOn) {
-        if (!h->useV3)
-            return fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction runs in the compact-code kernel only (solver seulex or Rosenbrock34, nEqn <= 64)");
-        if (h->dNActive && h->nActiveOff + n <= h->nActiveCap) B.nActive = h->dNActive + h->nActiveOff;
-    }
+    if (h->dacOn && !h->useV3)
+        return lb_fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction runs in the compact-code kernel only (solver seulex or Rosenbrock34, nEqn <= 64)");
     if (h->useV3) {
         long long grid3 = h->nSM;
         const long long need3 = (n + h->v3Groups - 1) / h->v3Groups;
         if (grid3 > need3) grid3 = need3;
-        if (grid3 < 1) grid3 = 1;
         CK(lb_v3_launch(h->opts.solver, (int)grid3, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, s));
         h->launches++;
         return LBCHEM_OK;
     }
-    if (h->useV2) {
-        long long grid2 = h->nSM;
-        const long long need2 = (n + h->v2Groups - 1) / h->v2Groups;
-        if (grid2 > need2) grid2 = need2;
-        if (grid2 < 1) grid2 = 1;
-        CK(lb_v2_launch(h->V2.nEqn, h->opts.solver, (int)grid2, h->v2Groups, h->v2Smem, h->V2, h->O, B, s));
+    // general kernel: one segment per launch, no dispatch order
+    for (int seg = 0; seg < 2; ++seg) {
+        BatchArgs B1 = B;
+        if (seg == 1) B1.a = B.b;
+        B1.b = CellSeg{}; B1.order = nullptr;
+        if (B1.a.n <= 0) continue;
+        if (seg == 1) CK(cudaMemsetAsync(queue, 0, sizeof(unsigned long long), s));
+        long long grid = (long long)h->nSM * h->ctasPerSM;
+        const long long need = (B1.a.n + h->groups - 1) / h->groups;
+        if (grid > need) grid = need;
+        CK(lb_launch_integrate(h->tpc, (int)grid, h->groups, h->smemBytes, (int)h->wsDoubles, h->M, h->O, B1, s));
         h->launches++;
-        return LBCHEM_OK;
     }
-    long long grid = (long long)h->nSM * h->ctasPerSM;
-    const long long need = (n + h->groups - 1) / h->groups;
-    if (grid > need) grid = need;
-    if (grid < 1) grid = 1;
-    CK(lb_launch_integrate(h->tpc, (int)grid, h->groups, h->smemBytes, (int)h->wsDoubles, h->M, h->O, B, s));
-    h->launches++;
     return LBCHEM_OK;
+}
+
+// sort_by_cost: counting sort of the queue positions by descending last cost (device), into the handle's order buffer
+int lb_cost_order(lbchem_handle h, const double* lastCost, long long n, cudaStream_t s, const int** orderOut) {
+    *orderOut = nullptr;
+    if (!h->useV3 || !lastCost || n < 2 || n > 0x7fffffffLL) return LBCHEM_OK;
+    if (n > h->orderCap) {
+        if (h->dOrder) cudaFree(h->dOrder);
+    if (h->dProbeIn) cudaFree(h->dProbeIn);
+    if (h->dProbeOut) cudaFree(h->dProbeOut);
+        h->dOrder = nullptr; h->orderCap = 0;
+        CK(cudaMalloc(&h->dOrder, (size_t)n * sizeof(int)));
+        h->orderCap = n;
+    }
+    if (!h->dHist) CK(cudaMalloc(&h->dHist, 4096 * sizeof(int)));
+    CK(lb_launch_cost_order(lastCost, n, h->opts.cost_model ? 0.125 : 1.0, h->dHist, h->dOrder, s));
+    h->launches += 3;
+    *orderOut = h->dOrder;
+    return LBCHEM_OK;
+}
+
+extern "C" {
+
+static CellSeg make_seg(long long n, long long ldy, const double* Y, const double* T, const double* p, const double* rho,
+                        const double* deltaT, double* deltaTChem, double* RR, double* Tout, double* cost, int32_t* status, int* nActive) {
+    CellSeg a{};
+    a.n = n; a.ldy = ldy; a.Y = Y; a.T = T; a.p = p; a.rho = rho; a.deltaT = deltaT; a.deltaTChem = deltaTChem; a.RR = RR;
+    a.Tout = Tout; a.cost = cost; a.status = status; a.nActive = nActive;
+    return a;
 }
 
 int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p,
@@ -594,9 +529,14 @@ int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy, const double* Y,
     { int rc = reserve_nactive(h, n); if (rc != LBCHEM_OK) return rc; }
     h->nActiveOff = 0;
     CK(cudaMemsetAsync(h->dStats, 0, 8 * sizeof(unsigned long long), s));
+    // sort_by_cost: `cost` holds the previous step's per-cell cost on entry (any finite values; zeros on a first step)
+    const int* order = nullptr;
+    if (h->opts.sort_by_cost && cost && n > 1) { int rc = lb_cost_order(h, cost, n, s, &order); if (rc != LBCHEM_OK) return rc; }
     CK(cudaEventRecord(h->ev0, s));
     if (n > 0) {
-        int rc = launch(h, n, ldy, Y, T, p, rho, deltaT, deltaT_uniform, deltaTChem, RR, Tout, cost, status, h->dQueue, s);
+        const CellSeg a = make_seg(n, ldy, Y, T, p, rho, deltaT, deltaTChem, RR, Tout, cost, status,
+                                   (h->dacOn && h->dNActive && n <= h->nActiveCap) ? h->dNActive : nullptr);
+        int rc = lb_launch_batch(h, &a, nullptr, deltaT_uniform, order, h->dQueue, h->dScratch, s);
         if (rc != LBCHEM_OK) return rc;
     }
     CK(cudaEventRecord(h->ev1, s));
@@ -611,6 +551,13 @@ static int slot_reserve(lbchem_handle h, Slot& s, long long cap, int nSp) {
         CK(cudaEventCreate(&s.k1));
         CK(cudaMalloc(&s.queue, sizeof(unsigned long long)));
     }
+    // every slot owns its work queue AND its kernel scratch: the kernels of consecutive chunks overlap on the device
+    if (h->useV3 && s.scratchCap < h->scratchCap) {
+        if (s.scratch) cudaFree(s.scratch);
+        s.scratch = nullptr; s.scratchCap = 0;
+        CK(cudaMalloc(&s.scratch, h->scratchCap));
+        s.scratchCap = h->scratchCap;
+    }
     if (cap <= s.cap) return LBCHEM_OK;
     void** ptrs[] = {(void**)&s.Y, (void**)&s.RR, (void**)&s.T, (void**)&s.p, (void**)&s.rho, (void**)&s.dT,
                      (void**)&s.dtc, (void**)&s.Tout, (void**)&s.cost, (void**)&s.status};
@@ -624,7 +571,8 @@ static int slot_reserve(lbchem_handle h, Slot& s, long long cap, int nSp) {
 }
 
 // Host-pointer entry point: cells are cut into chunks that cycle through kStreams streams, so the
-// H2D copy of chunk k+1 and the D2H copy of chunk k-1 overlap the integration of chunk k.
+// H2D copy of chunk k+1 and the D2H copy of chunk k-1 overlap the integration of chunk k (when the caller's
+// buffers are pinned; copies from pageable memory block the host and the chunks run one after the other).
 int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const double* T, const double* p,
                             const double* rho, const double* deltaT, double deltaT_uniform, double* deltaTChem, double* RR,
                             double* Tout, double* cost, int32_t* status) {
@@ -655,9 +603,9 @@ int lbchem_solve_batch_host(lbchem_handle h, int64_t n, int64_t ldy, const doubl
         if (deltaT) CK(cudaMemcpyAsync(s.dT, deltaT + c0, w, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(s.dtc, deltaTChem + c0, w, cudaMemcpyHostToDevice, st));
         if (!s.used) CK(cudaEventRecord(s.k0, st));
-        h->nActiveOff = c0;
-        rc = launch(h, m, s.cap, s.Y, s.T, s.p, s.rho, deltaT ? s.dT : nullptr, deltaT_uniform, s.dtc, s.RR, s.Tout, s.cost,
-                    s.status, s.queue, st);
+        const CellSeg a = make_seg(m, s.cap, s.Y, s.T, s.p, s.rho, deltaT ? s.dT : nullptr, s.dtc, s.RR, s.Tout, s.cost, s.status,
+                                   (h->dacOn && h->dNActive && c0 + m <= h->nActiveCap) ? h->dNActive + c0 : nullptr);
+        rc = lb_launch_batch(h, &a, nullptr, deltaT_uniform, nullptr, s.queue, s.scratch ? s.scratch : h->dScratch, st);
         if (rc != LBCHEM_OK) return rc;
         CK(cudaEventRecord(s.k1, st));
         s.used = true;
@@ -697,19 +645,40 @@ int lbchem_get_stats(lbchem_handle h, lbchem_stats* out) {
 // Test hook: evaluate derivatives / jacobian / LU-solve / rate constants for nItems states with the device
 // functions of the integrator. HOST pointers. Strides are in doubles (see probe_kernel for layouts).
 int lbchem_probe(lbchem_handle h, int32_t kind, int32_t nItems, const double* in, int32_t inStride, double* out, int32_t outStride) {
-    if (!h || !in || !out || nItems < 1 || kind < 0 || kind > LB_PROBE_RATES) return LBCHEM_E_INVALID;
+    if (!h || !in || !out || nItems < 1 || kind < 0 || kind > LBCHEM_PROBE_JAC_LUSOLVE) return LBCHEM_E_INVALID;
     CK(cudaSetDevice(h->device));
-    double *dIn = nullptr, *dOut = nullptr;
-    CK(cudaMalloc(&dIn, (size_t)nItems * inStride * 8));
-    CK(cudaMalloc(&dOut, (size_t)nItems * outStride * 8));
-    CK(cudaMemcpy(dIn, in, (size_t)nItems * inStride * 8, cudaMemcpyHostToDevice));
-    CK(cudaMemset(dOut, 0, (size_t)nItems * outStride * 8));
-    cudaError_t e = lb_launch_probe(h->tpc, h->groups, h->smemBytes, (int)h->wsDoubles, h->M, h->O, kind, nItems, dIn, dOut,
-                                    inStride, outStride, 0);
-    if (e == cudaSuccess) e = cudaDeviceSynchronize();
-    if (e == cudaSuccess) e = cudaMemcpy(out, dOut, (size_t)nItems * outStride * 8, cudaMemcpyDeviceToHost);
-    cudaFree(dIn); cudaFree(dOut);
-    if (e != cudaSuccess) return fail(h, LBCHEM_E_CUDA, std::string("probe: ") + cudaGetErrorString(e));
+    const bool v3 = h->useV3 && kind != LBCHEM_PROBE_LUSOLVE;
+    if (kind == LBCHEM_PROBE_JAC_LUSOLVE && !v3)
+        return fail(h, LBCHEM_E_UNSUPPORTED, "LBCHEM_PROBE_JAC_LUSOLVE probes the compact-code kernel (solver seulex or Rosenbrock34)");
+    // staging buffers are kept with the handle (test hook, but no allocation per call)
+    const size_t needIn = (size_t)nItems * inStride * 8, needOut = (size_t)nItems * outStride * 8;
+    if (needIn > h->probeInCap) { if (h->dProbeIn) cudaFree(h->dProbeIn); h->dProbeIn = nullptr; h->probeInCap = 0; CK(cudaMalloc(&h->dProbeIn, needIn)); h->probeInCap = needIn; }
+    if (needOut > h->probeOutCap) { if (h->dProbeOut) cudaFree(h->dProbeOut); h->dProbeOut = nullptr; h->probeOutCap = 0; CK(cudaMalloc(&h->dProbeOut, needOut)); h->probeOutCap = needOut; }
+    double *dIn = h->dProbeIn, *dOut = h->dProbeOut;
+    CK(cudaMemcpy(dIn, in, needIn, cudaMemcpyHostToDevice));
+    CK(cudaMemset(dOut, 0, needOut));
+    if (v3) {
+        BatchArgs B{};
+        B.scratch = h->dScratch; B.scratchStride = h->scratchStride;
+        long long grid = h->nSM;
+        const long long need = (nItems + h->v3Groups - 1) / h->v3Groups;
+        if (grid > need) grid = need;
+        CK(lb_v3_probe((int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, kind, nItems, dIn, inStride, dOut, outStride, 0));
+    } else {
+        CK(lb_launch_probe(h->tpc, h->groups, h->smemBytes, (int)h->wsDoubles, h->M, h->O, kind, nItems, dIn, dOut, inStride, outStride, 0));
+    }
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(out, dOut, needOut, cudaMemcpyDeviceToHost));
+    if (v3 && kind == LBCHEM_PROBE_RATES) {
+        // packed order -> mechanism order
+        const int nR = h->M.nR;
+        std::vector<double> tmp(2 * (size_t)nR);
+        for (int it = 0; it < nItems; ++it) {
+            double* o = out + (size_t)it * outStride;
+            std::copy(o, o + 2 * nR, tmp.begin());
+            for (int r = 0; r < nR; ++r) { o[r] = tmp[h->v3PosOf[r]]; o[nR + r] = tmp[nR + h->v3PosOf[r]]; }
+        }
+    }
     return LBCHEM_OK;
 }
 

@@ -57,20 +57,28 @@ struct DevOpts {
     double absTol, relTol, Treact, deltaTChemMax, cTauChem;
     int eqRateLimiter, dfdxIsDcdt;
     double RR, kcFloor;
+    int seulexErrOldMax, pad_;
 };
 
-// per-batch arguments
-struct BatchArgs {
+// one contiguous block of cells, field-major (the reference's cell list after pack: baseDataContainer.H:85-117)
+struct CellSeg {
     long long n, ldy;
     const double* Y; const double* T; const double* p; const double* rho; const double* deltaT;
-    double deltaTUniform;
     double* deltaTChem; double* RR; double* Tout; double* cost; int* status;
-    const int* order;            // optional processing order (descending last cost), may be null
+    int* nActive;                // optional: number of active species DAC kept for each cell (NsDAC_)
+};
+
+// per-batch arguments. A batch is one or two segments handed out through ONE work queue: the load-balanced step
+// integrates "own tail, then received cells" (reference LoadBalancedChemistryModel.C:608-611) in a single launch.
+struct BatchArgs {
+    CellSeg a, b;                // queue positions [0, a.n) -> segment a, [a.n, a.n + b.n) -> segment b
+    double deltaTUniform;
+    const int* order;            // optional dispatch order over the a.n + b.n queue positions (descending last cost), may be null
     unsigned long long* queue;   // work-queue head
     unsigned long long* stats;   // 8 counters: steps, attempts, jac, lu, solve, rhs, failed, cells
     double* scratch;             // v3 kernel: per-group global scratch (sparse Jacobian + seulex table), L2-resident
     int scratchStride;           // doubles per group
-    int* nActive;                // optional: number of active species DAC kept for each cell (NsDAC_)
+    int costModel;               // 0: cost = attempted sub-steps; 1: integer work units (see lbchem_options.cost_model)
 };
 
 // probe kinds (test hooks that run the same device functions as the integrator)

@@ -734,7 +734,7 @@ __device__ void seulex_solve(Grp<TPC>& g, const DevMech& M, const DevOpts& O, Wo
                 const double err = sqrt(g.sum(s) / n);
                 if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
                 if (err > 1 / LB_SMALL || (k > 1 && err >= errOld)) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
-                errOld = fmin(4 * err, 1.0);
+                errOld = O.seulexErrOldMax ? fmax(4 * err, 1.0) : fmin(4 * err, 1.0);
                 const double expo = 1.0 / (k + 1);
                 const double facmin = pow(stepFactor3, expo);
                 double fac;
@@ -987,20 +987,20 @@ __global__ void __launch_bounds__(TPC * 8) integrate_kernel(DevMech M, DevOpts O
             g.sync();
             q = reinterpret_cast<unsigned long long*>(g.red)[7];
         }
-        if (q >= (unsigned long long)B.n) break;
+        if (q >= (unsigned long long)B.a.n) break;
         const long long cell = B.order ? (long long)B.order[q] : (long long)q;
-        const double T0 = B.T[cell];
-        const double p0 = B.p[cell];
-        const double rho = B.rho[cell];
-        const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
-        double dtChem = B.deltaTChem[cell];
+        const double T0 = B.a.T[cell];
+        const double p0 = B.a.p[cell];
+        const double rho = B.a.rho[cell];
+        const double deltaT = B.a.deltaT ? B.a.deltaT[cell] : B.deltaTUniform;
+        double dtChem = B.a.deltaTChem[cell];
         w.nSteps = w.nAttempts = w.nJac = w.nLU = w.nSolve = w.nRhs = 0;
         Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1;
         int status;
         double Tend = T0;
         if (T0 > O.Treact) {
             g.sync();
-            for (int i = g.tid; i < nSp; i += TPC) w.Y0[i] = rho * B.Y[(size_t)i * B.ldy + cell] / M.W[i];
+            for (int i = g.tid; i < nSp; i += TPC) w.Y0[i] = rho * B.a.Y[(size_t)i * B.a.ldy + cell] / M.W[i];
             if (g.tid == 0) { w.Y0[nSp] = T0; w.Y0[nSp + 1] = p0; }
             g.sync();
             double timeLeft = deltaT;
@@ -1025,20 +1025,20 @@ __global__ void __launch_bounds__(TPC * 8) integrate_kernel(DevMech M, DevOpts O
             g.sync();
             dtChem = fmin(dtChem, O.deltaTChemMax);
             for (int i = g.tid; i < nSp; i += TPC) {
-                const double c0 = rho * B.Y[(size_t)i * B.ldy + cell] / M.W[i];
-                B.RR[(size_t)i * B.ldy + cell] = (w.Y0[i] - c0) * M.W[i] / deltaT;
+                const double c0 = rho * B.a.Y[(size_t)i * B.a.ldy + cell] / M.W[i];
+                B.a.RR[(size_t)i * B.a.ldy + cell] = (w.Y0[i] - c0) * M.W[i] / deltaT;
             }
             Tend = w.Y0[nSp];
             status = cs.fail ? cs.fail : LBCHEM_CELL_OK;
         } else {
-            for (int i = g.tid; i < nSp; i += TPC) B.RR[(size_t)i * B.ldy + cell] = 0.0;
+            for (int i = g.tid; i < nSp; i += TPC) B.a.RR[(size_t)i * B.a.ldy + cell] = 0.0;
             status = LBCHEM_CELL_SKIPPED;
         }
         if (g.tid == 0) {
-            B.deltaTChem[cell] = dtChem;
-            if (B.Tout) B.Tout[cell] = Tend;
-            if (B.cost) B.cost[cell] = (double)w.nAttempts;
-            if (B.status) B.status[cell] = status;
+            B.a.deltaTChem[cell] = dtChem;
+            if (B.a.Tout) B.a.Tout[cell] = Tend;
+            if (B.a.cost) B.a.cost[cell] = (double)w.nAttempts;
+            if (B.a.status) B.a.status[cell] = status;
             st_steps += w.nSteps; st_att += w.nAttempts; st_jac += w.nJac; st_lu += w.nLU;
             st_solve += w.nSolve; st_rhs += w.nRhs; st_fail += (status >= LBCHEM_CELL_MAX_STEPS); st_cells += 1;
         }

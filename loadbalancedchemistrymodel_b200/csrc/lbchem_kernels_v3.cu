@@ -919,7 +919,6 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
         attempts++;
         if (t == 0) CNT(CNT_ATTEMPTS)++;
         if (fabs(dx) < LB_VSMALL || attempts > 100000) { cs.fail = LBCHEM_CELL_UNDERFLOW; return; }
-        if (cs.kTarg + 1 > cx->tbRows) { cs.fail = LBCHEM_CELL_MAX_STEPS; return; }   // extrapolation table too small for this order
         double errOld = 0;
 #pragma unroll 1
         for (k = 0; k <= cs.kTarg + 1; ++k) {
@@ -945,7 +944,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
                 const double err = sqrt(g.sum(s, 1) / CNT(CNT_NODE));
                 if (!(err == err)) { cs.fail = LBCHEM_CELL_NAN; return; }
                 if (err > 1 / LB_SMALL || (k > 1 && err >= errOld)) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
-                errOld = fmin(4 * err, 1.0);
+                errOld = O.seulexErrOldMax ? fmax(4 * err, 1.0) : fmin(4 * err, 1.0);   // doubtful OpenFOAM detail: a switch
                 const double expo = 1.0 / (k + 1);
                 const double facmin = pow(stepFactor3, expo);
                 double fac;
@@ -1093,13 +1092,23 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         if (t == 0) reinterpret_cast<unsigned long long*>(WS(XS))[0] = atomicAdd(B.queue, 1ull);
         g.sync();
         const unsigned long long q = reinterpret_cast<unsigned long long*>(WS(XS))[0];
-        if (q >= (unsigned long long)B.n) break;
-        const long long cell = B.order ? (long long)B.order[q] : (long long)q;
-        const double T0 = B.T[cell];
-        const double p0 = B.p[cell];
-        const double rho = B.rho[cell];
-        const double deltaT = B.deltaT ? B.deltaT[cell] : B.deltaTUniform;
-        double dtChem = B.deltaTChem[cell];
+        if (q >= (unsigned long long)(B.a.n + B.b.n)) break;
+        // queue position -> (segment, cell): own cells first, then the cells received from other ranks
+        // (reference LoadBalancedChemistryModel.C:608-611), all through the one queue of this launch
+        long long cell = B.order ? (long long)B.order[q] : (long long)q;
+        const bool second = cell >= B.a.n;
+        if (second) cell -= B.a.n;
+#define SEG(f) (second ? B.b.f : B.a.f)
+        const double* __restrict__ Yp = SEG(Y);
+        double* __restrict__ RRp = SEG(RR);
+        const long long ldy = SEG(ldy);
+        const double T0 = SEG(T)[cell];
+        const double p0 = SEG(p)[cell];
+        const double rho = SEG(rho)[cell];
+        const double* dTp = SEG(deltaT);
+        const double deltaT = dTp ? dTp[cell] : B.deltaTUniform;
+        double* dtcp = SEG(deltaTChem);
+        double dtChem = dtcp[cell];
         if (t < CNT_N) CNT(t) = 0;
         Cell cs; cs.fail = 0; cs.theta = 0.0; cs.kTarg = 1; cs.f0valid = 0;
         if (t == 0) CNT(CNT_NODE) = cx->nEqn;
@@ -1107,14 +1116,14 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         double Tend = T0;
         double* y = VEC(0);
         if (T0 > O.Treact) {
-            if (t < nSp) y[t] = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t];
+            if (t < nSp) y[t] = rho * Yp[(size_t)t * ldy + cell] / S.W[t];
             if (t == nSp) y[nSp] = T0;
             if (t == nSp + 1) y[nSp + 1] = p0;
             g.sync();
             if (DAC) {
                 // LoadBalancedTDAC solveCell with mechRed()->active() (reference LoadBalancedTDACChemistryModel.C:385-393)
                 const int ns = dac_reduce(cx, base, y);
-                if (t == 0) { CNT(CNT_NODE) = ns + 2; if (B.nActive) B.nActive[cell] = ns; }
+                if (t == 0) { CNT(CNT_NODE) = ns + 2; int* na = SEG(nActive); if (na) na[cell] = ns; }
             }
             double timeLeft = deltaT;
             while (timeLeft > LB_SMALL) {
@@ -1128,25 +1137,30 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
             }
             dtChem = fmin(dtChem, O.deltaTChemMax);
             if (t < nSp) {
-                const double c0 = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t];
-                B.RR[(size_t)t * B.ldy + cell] = (y[t] - c0) * S.W[t] / deltaT;
+                const double c0 = rho * Yp[(size_t)t * ldy + cell] / S.W[t];
+                RRp[(size_t)t * ldy + cell] = (y[t] - c0) * S.W[t] / deltaT;
             }
             // the reduced call of the reference passes cData.T() for both T and p (:406-409): the aliased reference ends up
             // holding the p slot, i.e. the temperature the cell came in with
             Tend = DAC ? T0 : y[nSp];
             status = cs.fail ? cs.fail : LBCHEM_CELL_OK;
         } else {
-            if (t < nSp) B.RR[(size_t)t * B.ldy + cell] = 0.0;
+            if (t < nSp) RRp[(size_t)t * ldy + cell] = 0.0;
             status = LBCHEM_CELL_SKIPPED;
         }
         if (t == 0) {
-            B.deltaTChem[cell] = dtChem;
-            if (B.Tout) B.Tout[cell] = Tend;
-            if (B.cost) B.cost[cell] = (double)CNT(CNT_ATTEMPTS);
-            if (B.status) B.status[cell] = status;
+            dtcp[cell] = dtChem;
+            double* To = SEG(Tout); double* co = SEG(cost); int* so = SEG(status);
+            if (To) To[cell] = Tend;
+            // per-cell cost (the reference stores wall-clock seconds, LoadBalancedChemistryModel.C:431-448): attempted
+            // sub-steps, or integer work units weighted by what each building block costs on this kernel
+            if (co) co[cell] = B.costModel ? (double)(9 * CNT(CNT_LU) + CNT(CNT_SOLVE) + 3 * CNT(CNT_RHS) + 12 * CNT(CNT_JAC))
+                                           : (double)CNT(CNT_ATTEMPTS);
+            if (so) so[cell] = status;
             st[0] += CNT(CNT_STEPS); st[1] += CNT(CNT_ATTEMPTS); st[2] += CNT(CNT_JAC); st[3] += CNT(CNT_LU);
             st[4] += CNT(CNT_SOLVE); st[5] += CNT(CNT_RHS); st[6] += (status >= LBCHEM_CELL_MAX_STEPS); st[7] += 1;
         }
+#undef SEG
     }
     if (t == 0 && st[7]) {
 #pragma unroll
@@ -1185,12 +1199,12 @@ __global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, 
     const SMech& S = cx->S;
     const int nSp = S.nSp, nR = S.nR, t = g.tid;
     const long long groups = (long long)gridDim.x * cx->groups;
-    for (long long cell = (long long)blockIdx.x * cx->groups + threadIdx.x / TPC; cell < B.n; cell += groups) {
+    for (long long cell = (long long)blockIdx.x * cx->groups + threadIdx.x / TPC; cell < B.a.n; cell += groups) {
         g.sync();
         double* y = VEC(0);
-        const double T = B.T[cell], rho = B.rho[cell];
+        const double T = B.a.T[cell], rho = B.a.rho[cell];
         double c = 0.0;
-        if (t < nSp) { c = rho * B.Y[(size_t)t * B.ldy + cell] / S.W[t]; y[t] = c; }
+        if (t < nSp) { c = rho * B.a.Y[(size_t)t * B.a.ldy + cell] / S.W[t]; y[t] = c; }
         g.sync();
         const double cSum = g.sum(c, 3);          // the reference sums the unclamped concentrations
         const double lnT = log(T), invT = 1.0 / T;
@@ -1211,19 +1225,90 @@ __global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, 
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Test hook (lbchem_probe): the building blocks of THIS kernel -- prepare / reaction_sweep / derivatives / jacobian /
+// lu_factor / lu_solve, the very device functions integrate_v3_kernel calls -- on single states, so that a parity failure
+// can be localised. One state per 64-thread group. Layouts as in include/lbchem.h (kf / kr come out in packed reaction
+// order; the host maps them back).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TPC * 6, 1) probe_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, int kind, int nItems,
+                                                              const double* in, int inStride, double* out, int outStride) {
+    extern __shared__ double smem[];
+    unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
+    {
+        const unsigned long long* src = reinterpret_cast<const unsigned long long*>(M.blob);
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(sm + CTX_BYTES);
+        for (int i = threadIdx.x; i < M.hotBytes / 8; i += blockDim.x) dst[i] = src[i];
+    }
+    Ctx* cxw = reinterpret_cast<Ctx*>(sm);
+    if (threadIdx.x == 0) {
+        bind(cxw->S, M, sm + CTX_BYTES);
+        bind_cold(cxw->S, M);
+        cxw->O = O;
+        cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
+        cxw->wsDoubles = ctx_layout(*cxw, M);
+        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
+        cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
+    }
+    __syncthreads();
+    const Ctx* cx = cxw;
+    double* base = reinterpret_cast<double*>(sm + CTX_BYTES + M.hotBytes) + (size_t)(threadIdx.x / TPC) * wsDoubles;
+    const Grp g(base);
+    const SMech& S = cx->S;
+    const int nSp = S.nSp, nR = S.nR, t = g.tid, N = cx->nEqn;
+    const int groups = gridDim.x * cx->groups;
+    for (int item = blockIdx.x * cx->groups + threadIdx.x / TPC; item < nItems; item += groups) {
+        const double* x = in + (size_t)item * inStride;
+        double* o = out + (size_t)item * outStride;
+        g.sync();
+        if (t < CNT_N) CNT(t) = 0;
+        if (t == 0) CNT(CNT_NODE) = N;
+        double* y = VEC(0);
+        if (t < N) y[t] = x[t];
+        g.sync();
+        if (kind == LBCHEM_PROBE_DERIV) {
+            derivatives<false>(cx, base, y, VEC(1));
+            if (t < N) o[t] = VEC(1)[t];
+        } else if (kind == LBCHEM_PROBE_RATES) {
+            const double T = y[nSp], lnT = log(T), invT = 1.0 / T;
+            prepare(g, cx, base, y, T, lnT, true);
+            reaction_sweep<false>(cx, base, 1, T, lnT, invT);
+            const double* KF = WS(A);
+            for (int p = t; p < 2 * nR; p += TPC) o[p] = KF[p];
+        } else {
+            jacobian<false>(cx, base, y, VEC(8), nullptr);
+            if (kind == LBCHEM_PROBE_JAC) {
+                if (t < N) o[t] = VEC(8)[t];
+                double* J = o + N;
+                for (int k = t; k < N * N; k += TPC) J[k] = 0.0;
+                g.sync();
+                if (t < nSp) {
+                    const double* JS = GS_JS;
+                    for (int e = S.rowPtr[t]; e < S.rowPtr[t + 1]; ++e) J[t * N + S.entCol[e]] = JS[e];
+                    J[t * N + nSp] = WS(JT)[t];
+                }
+            } else {                                   // LBCHEM_PROBE_JAC_LUSOLVE: x = (dg I - J(y))^-1 b
+                const double dg = x[N];
+                const int st = lu_factor<false>(cx, base, dg);
+                double* b = VEC(1);
+                if (t < N) b[t] = x[N + 1 + t];
+                lu_solve<false>(cx, base, b);
+                if (t < N) o[t] = st ? __longlong_as_double(0x7ff8000000000000LL) : b[t];
+            }
+        }
+        g.sync();
+    }
+}
+
 }  // namespace v3
 
 // ------------------------------------------------------------------------------------------------
 // host side: workspace size (must match v3::ctx_layout), configuration, launch
 // ------------------------------------------------------------------------------------------------
 int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol) {
-    int tb = 0;
-    if (solver == LBCHEM_SOLVER_SEULEX) {
-        int kt = (int)(-log10(relTol + absTol) * 0.6 + 0.5);
-        kt = kt < 1 ? 1 : (kt > 10 ? 10 : kt);
-        tb = kt + 4 < 11 ? kt + 4 : 11;
-    }
-    M.tbRows = tb;
+    // the extrapolation table lives in the global scratch, always sized for the reference's full kMaxx = 11 rows
+    (void)relTol; (void)absTol;
+    M.tbRows = solver == LBCHEM_SOLVER_SEULEX ? 11 : 0;
     v3::Ctx c;
     return v3::ctx_layout(c, M);
 }
@@ -1267,3 +1352,12 @@ cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, cons
     return cudaGetLastError();
 }
 
+
+cudaError_t lb_v3_probe(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+                        int kind, int nItems, const double* in, int inStride, double* out, int outStride, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(v3::probe_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (e != cudaSuccess) return e;
+    V2Mech Mm = M; Mm.dac = nullptr;
+    v3::probe_v3_kernel<<<grid, groups * v3::TPC, smemBytes, s>>>(Mm, O, B, wsDoubles, kind, nItems, in, inStride, out, outStride);
+    return cudaGetLastError();
+}

@@ -144,7 +144,7 @@ int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32
     return 0;
 }
 
-int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err) {
+int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err, std::vector<int>* posOfOut) {
     const int nSp = m->n_species, nR = m->n_reactions, nEff = m->n_eff;
     const int N = nSp + 2;
     if (N > 64 || nSp > 254 || nR > 32000 || nEff > 31 || nR < 1) return 1;
@@ -154,6 +154,7 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     // ---- reaction order: homogeneous rounds of 64 (exp / no exp / irreversible / third body / fall-off)
     std::vector<int> order, posOf;
     reaction_order(m, order, posOf);
+    if (posOfOut) *posOfOut = posOf;
 
     std::vector<double> tcTab;
     std::vector<double> A(nR), beta(nR), Ta(nR), fall;

@@ -1257,7 +1257,7 @@ int oracle_solve_batch(const oracle_mech* M, const lbchem_options* opts, int seu
     oracle_opts O;
     memset(&O, 0, sizeof(O));
     O.o = *opts;
-    O.seulex_errold_max = seulex_errold_max;
+    O.seulex_errold_max = seulex_errold_max || opts->seulex_errold_max;
     O.dac_active = g_dac.active; O.dac_tol = g_dac.tol; O.dac_ninit = g_dac.ninit;
     memcpy(O.dac_init, g_dac.init, sizeof(O.dac_init));
     if (nthreads < 1) nthreads = 1;

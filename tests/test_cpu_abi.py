@@ -53,12 +53,15 @@ def test_struct_layouts_match_header(lib):
     """sizeof of the ctypes mirrors equals what the C compiler lays out for include/lbchem.h."""
     import subprocess
     import tempfile
-    src = '#include <stdio.h>\n#include "lbchem.h"\nint main(){printf("%zu %zu %zu\\n", sizeof(lbchem_mech_desc), sizeof(lbchem_options), sizeof(lbchem_stats));return 0;}\n'
+    src = ('#include <stdio.h>\n#include "lbchem.h"\nint main(){printf("%zu %zu %zu %zu %zu %zu %zu\\n", sizeof(lbchem_mech_desc), '
+           'sizeof(lbchem_options), sizeof(lbchem_stats), sizeof(lbchem_lb_options), sizeof(lbchem_lb_info), sizeof(lbchem_p2p_op), '
+           'sizeof(lbchem_transport));return 0;}\n')
     with tempfile.TemporaryDirectory() as d:
         (Path(d) / "s.c").write_text(src)
         subprocess.check_call(["gcc", "-I", str(ROOT / "include"), str(Path(d) / "s.c"), "-o", str(Path(d) / "s")])
         out = subprocess.check_output([str(Path(d) / "s")]).decode().split()
-    assert [int(x) for x in out] == [C.sizeof(capi.MechDesc), C.sizeof(capi.Options), C.sizeof(capi.Stats)]
+    assert [int(x) for x in out] == [C.sizeof(capi.MechDesc), C.sizeof(capi.Options), C.sizeof(capi.Stats), C.sizeof(capi.LbOptions),
+                                     C.sizeof(capi.LbInfo), C.sizeof(capi.P2POp), C.sizeof(capi.Transport)]
 
 
 def test_no_cpu_fallback(lib, gri):
@@ -78,7 +81,11 @@ def test_missing_library_fails_loudly(tmp_path):
 def test_product_never_imports_oracle():
     """The oracle is test infrastructure: nothing under the package may import, link or dlopen it."""
     pkg = ROOT / "loadbalancedchemistrymodel_b200"
-    for f in list(pkg.rglob("*.py")) + list(pkg.rglob("*.cu")) + list(pkg.rglob("*.cpp")) + list(pkg.rglob("*.cuh")) + list(pkg.rglob("Makefile")):
+    files = []
+    for pat in ("*.py", "*.cu", "*.cpp", "*.cuh", "*.hpp", "Makefile"):
+        files += list(pkg.rglob(pat))
+    files += list((ROOT / "adapter").rglob("*.H")) + list((ROOT / "include").rglob("*.h"))
+    for f in files:
         t = f.read_text()
         assert "lbchem_oracle" not in t and "from oracle" not in t and "import oracle" not in t, f
 
@@ -87,3 +94,17 @@ def test_plan_and_cells_to_send_run_on_host(lib):
     send, recv = capi.balance_plan(np.array([4.0, 1.0, 1.0, 2.0]), np.array([10, 10, 10, 10]))
     assert send[0] and not send[1] and not send[2]
     assert capi.cells_to_send(np.ones(10), 3.0, 0) == 3
+
+
+def test_lb_defaults_and_host_build(lib):
+    """LoadBalancedCoeffs defaults (reference LoadBalancedChemistryModel.C:41-45) and the CPU test build of the step."""
+    o = capi.LbOptions()
+    lib.lbchem_lb_default_options(C.byref(o))
+    assert o.update_iter == 0 and o.min_fraction == 0.02 and o.tdac == 0 and o.balance == 1
+    host = capi.load_lbhost()
+    for sym in ("lbchem_lbhost_create", "lbchem_lb_solve", "lbchem_lb_get_info", "lbchem_lb_get_plan", "lbchem_lb_destroy"):
+        assert hasattr(host, sym)
+    # NCCL is resolved at run time: the library itself must not depend on libnccl at load time
+    import subprocess
+    needed = subprocess.check_output(["readelf", "-d", str(capi.LIB_PATH)]).decode()
+    assert "libnccl" not in needed

@@ -3,8 +3,9 @@
 Covers what the reference's own tests leave out (SURVEY section 4 "gaps": only its firstTime_ branch ever runs):
 redistribution must not change results, messages return in the same order and size
 (reference tests/src/pointToPointBuffer-Test.C:73-290 checks that for raw label lists), updateIter > 0.
-The cell "solver" here is a deterministic stand-in (the CUDA library needs a GPU); the driver under test is
-the product's loadbalancedchemistrymodel_b200/model.py.
+The cell "solver" here is a deterministic stand-in (the CUDA library needs a GPU). The step logic under test is the
+product's C++ driver, csrc/lbchem_lb_core.hpp -- the same source liblbchem.so runs on the device -- compiled for host
+memory (liblbchem_lbhost.so) with gloo behind its transport callbacks (model.HostStepModel).
 """
 import os
 import socket
@@ -17,7 +18,7 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 from loadbalancedchemistrymodel_b200 import capi
-from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel, cells_to_send_device
+from loadbalancedchemistrymodel_b200.model import HostStepModel
 
 NSP = 5
 
@@ -44,7 +45,7 @@ def make_state(rank, n, seed=0):
     return Y, T, p, rho, dtc
 
 
-def _worker(rank, world, port, n, update_iter, host_c2s, lts, q):
+def _worker(rank, world, port, n, update_iter, tdac, lts, q):
     try:
         os.environ["MASTER_ADDR"] = "127.0.0.1"
         os.environ["MASTER_PORT"] = str(port)
@@ -52,9 +53,8 @@ def _worker(rank, world, port, n, update_iter, host_c2s, lts, q):
         nloc = n + 13 * rank                      # ragged shard sizes
         Y, T, p, rho, dtc0 = make_state(rank, nloc)
         dT = (1e-6 * (1.0 + torch.arange(nloc, dtype=torch.float64) / nloc)) if lts else 1e-6
-        model = LoadBalancedChemistryModel(NSP, fake_solver, "cpu", update_iter=update_iter, host_cells_to_send=host_c2s)
-        single = LoadBalancedChemistryModel(NSP, fake_solver, "cpu")
-        single.world = 1                          # never exchanges: the reference's non-load-balanced model
+        model = HostStepModel(NSP, fake_solver, update_iter=update_iter, tdac=tdac)
+        single = HostStepModel(NSP, fake_solver, balance=False, tdac=tdac)   # never exchanges: the non-load-balanced model
         out = []
         dtc_lb, dtc_ref = dtc0, dtc0
         for step in range(4):
@@ -65,7 +65,11 @@ def _worker(rank, world, port, n, update_iter, host_c2s, lts, q):
                   and torch.equal(model.status, single.status) and m1 == m2)
             out.append(dict(step=step, ok=bool(ok), last={k: v for k, v in model.last.items()},
                             send=list(model.send_plan), recv=list(model.recv_plan), total=model.total_cost))
-            dtc_lb, dtc_ref = model.deltaTChem, single.deltaTChem
+            if not tdac:                          # LoadBalancedTDAC never writes deltaTChem back (reference TDAC .C:968-971)
+                dtc_lb, dtc_ref = model.deltaTChem, single.deltaTChem
+            else:
+                ok = ok and torch.equal(model.deltaTChem, dtc0)
+                out[-1]["ok"] = bool(ok)
         q.put((rank, out, None))
         dist.barrier()
         dist.destroy_process_group()
@@ -78,11 +82,11 @@ def _free_port():
     return port
 
 
-def _run(world, n=400, update_iter=0, host_c2s=False, lts=False):
+def _run(world, n=400, update_iter=0, tdac=False, lts=False):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, update_iter, host_c2s, lts, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, update_iter, tdac, lts, q)) for r in range(world)]
     for p_ in procs:
         p_.start()
     res = {}
@@ -95,9 +99,9 @@ def _run(world, n=400, update_iter=0, host_c2s=False, lts=False):
     return res
 
 
-@pytest.mark.parametrize("world,host_c2s,lts", [(2, False, False), (2, True, True), (4, False, True)])
-def test_redistribution_preserves_results_and_order(world, host_c2s, lts):
-    res = _run(world, host_c2s=host_c2s, lts=lts)
+@pytest.mark.parametrize("world,tdac,lts", [(2, False, False), (2, True, True), (4, False, True), (4, True, False)])
+def test_redistribution_preserves_results_and_order(world, tdac, lts):
+    res = _run(world, tdac=tdac, lts=lts)
     for rank, out in res.items():
         assert all(o["ok"] for o in out), (rank, out)
         assert out[0]["last"]["sent_cells"] == 0 and not out[0]["last"]["planned"]      # firstTime_: all local
@@ -118,15 +122,14 @@ def test_update_iter_replans_every_third_step():
     assert all(o["ok"] for o in res[0]) and all(o["ok"] for o in res[1])
 
 
-def test_cells_to_send_device_scan_matches_sequential_loop():
-    rng = np.random.default_rng(5)
-    for _ in range(200):
-        n = int(rng.integers(0, 60))
-        cost = rng.integers(0, 30, n).astype(np.float64)
-        excl = torch.zeros(n + 1, dtype=torch.float64)
-        if n:
-            excl[1:] = torch.cumsum(torch.from_numpy(cost), 0)
-        start = int(rng.integers(0, n + 2))
-        target = float(rng.integers(0, 200)) * float(rng.choice([1.0, 0.37]))
-        want = capi.cells_to_send(cost, target, min(start, n))
-        assert cells_to_send_device(excl, target, min(start, n)) == want
+def test_single_rank_without_process_group():
+    """world 1: every step is the local branch, deltaTChem is carried, the total cost is the sum of the cell costs."""
+    Y, T, p, rho, dtc0 = make_state(0, 97)
+    m = HostStepModel(NSP, fake_solver)
+    m1 = m.solve(Y, T, p, rho, 1e-6, dtc0)
+    assert m.last["sent_cells"] == 0 and not m.last["exchanged"]
+    assert m.total_cost == float(m.cell_cost.sum()) and m1 == float(m.deltaTChem.min())
+    m.solve(Y, T, p, rho, 1e-6)
+    assert torch.equal(m.deltaTChem, dtc0 * 0.25)
+    e = m.solve(Y[:, :0], T[:0], p[:0], rho[:0], 1e-6, dtc0[:0])       # a rank without cells (reference .C:455: GREAT)
+    assert e == 1e15 and m.RR.shape == (NSP, 0)

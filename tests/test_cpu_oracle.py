@@ -215,3 +215,30 @@ def test_oracle_regression_vector(gri, flame):
         assert np.allclose(r["deltaTChem"], z[f"{solver}_deltaTChem"], rtol=1e-9, atol=0)
         ref = z[f"{solver}_RR"]
         assert np.allclose(r["RR"], ref, rtol=1e-8, atol=1e-12 * np.abs(ref).max())
+
+
+def test_last_substep_coin_toss_belongs_to_the_algorithm(gri):
+    """ODESolver::solve ends with dx = xEnd - x; whether x + dx then equals xEnd to the last bit decides if one more
+    ~1e-22 s sub-step is taken. That is round-off of the reference algorithm, not of an implementation: the
+    oracle ITSELF changes the attempt count of about 1 % of hot cells when deltaT, T or deltaTChem move by one ulp, the
+    state (RR) stays put and the returned sub-step guess jumps by the same factors (~0.26 / ~3.8) the GPU parity test
+    sees in its 'cells with a different attempt count' (tests/test_gpu_parity.py::_compare bounds them with this evidence)."""
+    from loadbalancedchemistrymodel_b200 import capi, workloads as W
+    mech, Y, T, p, rho = W.gri_uniform(1000)
+    om = O.OracleModel(mech, capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1))
+    r0 = om.solve_batch(Y, T, p, rho, 1e-6, 1e-7, nthreads=8)
+    flipped, ratios = 0, []
+    for args in ((Y, T, p, rho, np.nextafter(1e-6, 1), 1e-7), (Y, np.nextafter(T, 1e9), p, rho, 1e-6, 1e-7),
+                 (Y, T, p, rho, 1e-6, np.nextafter(1e-7, 1))):
+        r1 = om.solve_batch(*args, nthreads=8)
+        d = r1["attempts"] != r0["attempts"]
+        flipped += int(d.sum())
+        ratios += list(r1["deltaTChem"][d] / r0["deltaTChem"][d])
+        assert (np.abs(r1["attempts"] - r0["attempts"])[d] == 1).all()
+        eRR = np.abs(r1["RR"] - r0["RR"]) / (np.abs(r0["RR"]) + 1e-12 * mech.W[:, None] / 1e-6)
+        assert eRR.max() < 1e-8                                    # same state in every cell, flipped or not
+        same = ~d
+        assert (np.abs(r1["deltaTChem"][same] / r0["deltaTChem"][same] - 1)).max() < 1e-9
+    ratios = np.array(ratios)
+    print("cells flipped by one-ulp input changes:", flipped, "of", 3 * 1000, "deltaTChem ratios", np.round(np.sort(ratios), 3))
+    assert flipped >= 10 and ratios.min() > 0.1 and ratios.max() < 10.0

@@ -36,20 +36,33 @@ def _compare(mech, Y, rho, got, ref, dt, tag, abs_tol=1e-12, max_other_count=0.0
     eR = np.abs(got["RR"] - ref["RR"]) / (np.abs(ref["RR"]) + abs_tol * W / np.asarray(dt))
     same = got["cost"] == ref["attempts"]
     eD = np.abs(got["deltaTChem"] - ref["deltaTChem"])[same] / ref["deltaTChem"][same]
+    other = ~same
+    ratio = got["deltaTChem"][other] / ref["deltaTChem"][other]
+    dA = (got["cost"] - ref["attempts"])[other]
     print(f"{tag}: max rel err Y {eY.max():.2e} T {eT.max():.2e} RR {eR.max():.2e} dtChem {eD.max():.2e} "
-          f"cells with a different attempt count {int((~same).sum())}/{same.size}")
+          f"cells with a different attempt count {int(other.sum())}/{same.size}"
+          + (f" (attempt difference {np.unique(dA)}, deltaTChem ratio there {ratio.min():.3f} .. {ratio.max():.3f})" if other.any() else ""))
     assert eY.max() < RTOL and eT.max() < RTOL and eR.max() < RTOL and eD.max() < 1e-5
-    # The last sub-step is dx = xEnd - x; whether x + dx == xEnd exactly is a round-off coin toss of the
-    # reference algorithm itself (one more ~1e-22 s step, other deltaTChem, same state): allow 1 % of cells.
+    # The last sub-step is dx = xEnd - x; whether x + dx lands on xEnd exactly is a round-off coin toss of the reference
+    # algorithm itself: the oracle flips the same way in 1.1-1.5 % of these cells when deltaT, T or deltaTChem move by ONE
+    # ulp (tests/test_cpu_oracle.py::test_last_substep_coin_toss_belongs_to_the_algorithm). A flipped cell takes one
+    # ~1e-22 s sub-step more or less: same state (Y, T, RR are checked above for ALL cells), and the returned sub-step
+    # guess is the proposal of the other branch of ODESolver::solve, a factor 0.26 or 3.8 away in the oracle's
+    # own flips. Bounded here, not masked:
     assert (~same).mean() <= max_other_count
+    if other.any():
+        assert (np.abs(dA) == 1).all() and ratio.min() > 0.1 and ratio.max() < 10.0
     return eY.max(), eT.max(), eR.max()
 
 
-def test_probes_match_oracle(gri, flame):
-    """derivatives / jacobian / rate constants / LU of the device code against the oracle, state by state."""
+@pytest.mark.parametrize("kernel", ["v3", "general"])
+def test_probes_match_oracle(gri, flame, kernel):
+    """derivatives / jacobian / rate constants / LU of the device code against the oracle, state by state: the device
+    functions of the PRODUCTION compact-code kernel (v3: prepare, reaction_sweep, derivatives, jacobian, lu_factor,
+    lu_solve) and, as a second column, those of the general kernel (threads_per_cell = 64)."""
     sel = np.argsort(-flame["T"])[::40][:64]
     Y, T, p, rho = _state(gri, flame, sel)
-    opts = capi.default_options(solver="Rosenbrock34", abs_tol=1e-12, rel_tol=1e-2)
+    opts = capi.default_options(solver="Rosenbrock34", abs_tol=1e-12, rel_tol=1e-2, threads_per_cell=0 if kernel == "v3" else 64)
     chem = capi.Chemistry(gri, opts)
     om = O.OracleModel(gri, opts)
     n = gri.n_species + 2
@@ -70,32 +83,43 @@ def test_probes_match_oracle(gri, flame):
         assert np.allclose(Jg[:, :-2], J[:, :-2], rtol=1e-9, atol=1e-12 * np.abs(J).max()), k
         assert np.allclose(Jg[:, -2], J[:, -2], rtol=1e-6, atol=1e-9 * np.abs(J[:, -2]).max()), k
     # LU solve of I/(gamma dx) - J
-    items = []
-    for k in range(8):
-        _, J = om.jacobian(y[k])
-        A = -J + np.eye(n) / (0.5 * 1e-7)
-        b = om.derivatives(y[k])
-        items.append(np.concatenate([A.ravel(), b]))
-    x = chem.probe(capi.PROBE_LUSOLVE, np.array(items))
-    for k in range(8):
-        A = items[k][: n * n].reshape(n, n); b = items[k][n * n:]
-        st, xr = O.lu_solve(A, b)
-        assert st == 0
-        assert np.allclose(x[k], xr, rtol=1e-9, atol=1e-13 * np.abs(xr).max()), k
+    dg = 1.0 / (0.5 * 1e-7)
+    if kernel == "general":
+        items = []
+        for k in range(8):
+            _, J = om.jacobian(y[k])
+            A = -J + np.eye(n) * dg
+            b = om.derivatives(y[k])
+            items.append(np.concatenate([A.ravel(), b]))
+        x = chem.probe(capi.PROBE_LUSOLVE, np.array(items))
+        for k in range(8):
+            A = items[k][: n * n].reshape(n, n); b = items[k][n * n:]
+            st, xr = O.lu_solve(A, b)
+            assert st == 0
+            assert np.allclose(x[k], xr, rtol=1e-9, atol=1e-13 * np.abs(xr).max()), k
+    else:
+        # the compact-code kernel factorises what its own jacobian() left in the sparse store: probe the chain
+        # jacobian -> lu_factor -> lu_solve against LUDecompose / LUBacksubstitute of the oracle on dg I - J_oracle
+        items, want = [], []
+        for k in range(16):
+            _, J = om.jacobian(y[k])
+            b = om.derivatives(y[k])
+            items.append(np.concatenate([y[k], [dg], b]))
+            st, xr = O.lu_solve(-J + np.eye(n) * dg, b)
+            assert st == 0
+            want.append(xr)
+        x = chem.probe(capi.PROBE_JAC_LUSOLVE, np.array(items))
+        for k in range(16):
+            assert np.allclose(x[k], want[k], rtol=1e-8, atol=1e-12 * np.abs(want[k]).max()), k
     chem.close()
 
 
-@pytest.mark.parametrize("kernel", ["v3", "v2", "general"])
+@pytest.mark.parametrize("kernel", ["v3", "general"])
 @pytest.mark.parametrize("solver,rel_tol", [("Rosenbrock34", 1e-2), ("seulex", 1e-1)])
 def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol, kernel, monkeypatch):
     """All 4000 cells of the reference's flame fixture, both tolerance sets of BASELINE config 3, through the
-    compact-code kernel (v3, default), the register-LU kernel (LBCHEM_KERNEL=v2) and the general kernel
-    (threads_per_cell = 64)."""
+    compact-code kernel (v3, default) and the general kernel (threads_per_cell = 64)."""
     tpc = 64 if kernel == "general" else 0
-    if kernel == "v2":
-        monkeypatch.setenv("LBCHEM_KERNEL", "v2")
-    else:
-        monkeypatch.delenv("LBCHEM_KERNEL", raising=False)
     sel = np.arange(flame["T"].shape[0])
     Y, T, p, rho = _state(gri, flame, sel)
     opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, threads_per_cell=tpc)
@@ -150,19 +174,35 @@ def test_ch4_one_step_parity(solver):
     assert (got["status"] == ref["status"]).all() and same.all()
     assert (np.abs(Yg - Yr) / (np.abs(Yr) + 1e-12 * W_ / rho)).max() < RTOL
     assert (np.abs(got["T"] - ref["T"]) / ref["T"]).max() < RTOL
-    # RR against the cell's own rate scale: in hot lean cells the algorithm burns CH4 down to ~1e-15 kmol/m3 in
-    # ~40 chemistry-limited sub-steps; that residue is round-off of the 5x5 solve (absolute ~1e-19), so quantities
-    # proportional to 1/c_CH4 -- the returned deltaTChem = c_O2 / (2 pf c_CH4) -- carry 1e-3 relative noise in the
-    # REFERENCE algorithm itself (a single sub-step, deltaT = 1e-9, agrees to 8e-15; scripts/diag_euler.py).
+    # RR = (c - c0) W / deltaT: where nothing reacts (cold cells) c - c0 is the round-off of c itself, eps*|c0|*W/deltaT in
+    # RR units, which no implementation of the reference formula can beat -- the ORACLE's own RR moves by 6.9e-6 of the 1e-6
+    # floor when rho changes by one ulp (shown below). The bound is therefore 1e-6 relative (north_star) plus that
+    # representation noise, nothing wider.
+    eps = np.finfo(float).eps
+    c0 = rho * Y / W_
+    noise = 8 * eps * c0 * W_ / DT
     scale = np.abs(ref["RR"]).max(0, keepdims=True)
-    eRR = (np.abs(got["RR"] - ref["RR"]) / (scale + 1e-12 * W_ / DT)).max()
-    print(solver, "max RR error relative to the cell's rate scale", eRR)
-    assert eRR < (1e-5 if solver == "EulerImplicit" else RTOL)     # EulerImplicit: 7e-6 measured, open item
+    excess = np.abs(got["RR"] - ref["RR"]) - noise
+    eRR = (np.maximum(excess, 0.0) / (scale + 1e-12 * W_ / DT)).max()
+    print(solver, "max RR error beyond the representation noise, relative to the cell's rate scale", eRR)
+    assert eRR < RTOL
     eD = np.abs(got["deltaTChem"] - ref["deltaTChem"]) / ref["deltaTChem"]
     if solver != "EulerImplicit":
         assert eD.max() < 1e-5
         return
-    assert eD.max() < 1e-2 and np.median(eD) < 1e-12 and (eD > 1e-9).mean() < 0.03
+    # EulerImplicit returns deltaTChem = cTauChem * tMin with tMin ~ c_O2 / (2 pf c_CH4): in hot lean cells the algorithm
+    # burns CH4 down to ~1e-15 kmol/m3, where that quotient amplifies the last bits of the 5x5 solve. How much is a
+    # property of the reference algorithm: measure it on the oracle itself (inputs moved by ONE ulp) and hold the GPU to it.
+    om = O.OracleModel(mech, opts)
+    self_d, self_rr = 0.0, 0.0
+    for args in ((Y, T, p, np.nextafter(rho, 1e9)), (np.nextafter(Y, 2.0), T, p, rho), (Y, np.nextafter(T, 1e9), p, rho)):
+        r1 = om.solve_batch(*args, DT, DTCHEM, nthreads=8)
+        self_d = max(self_d, (np.abs(r1["deltaTChem"] - ref["deltaTChem"]) / ref["deltaTChem"]).max())
+        self_rr = max(self_rr, (np.abs(r1["RR"] - ref["RR"]) / (scale + 1e-12 * W_ / DT)).max())
+    print(f"EulerImplicit: oracle moves under one-ulp input changes by deltaTChem {self_d:.2e}, RR {self_rr:.2e} of the floor; "
+          f"GPU vs oracle deltaTChem {eD.max():.2e}")
+    assert self_rr > 1e-6                                  # the oracle itself leaves the naive 1e-6 band in cold cells
+    assert eD.max() < 10 * self_d and np.median(eD) < 1e-12 and (eD > 1e-9).mean() < 0.03
     one = capi.Chemistry(mech, opts)
     g1 = one.solve_host(Y, T, p, rho, 1e-9, DTCHEM)
     one.close()
@@ -194,17 +234,19 @@ def test_edge_cases(gri, flame):
 
 
 def test_driver_on_one_gpu_equals_direct_call(gri, flame):
-    """The host driver (model.py) with the CUDA cell solver, world size 1: same fields as the C ABI call, and the
-    second step starts from the first step's deltaTChem (reference .C:130,398,490)."""
+    """lbchem_lb_solve with one rank (the library's load-balanced entry point over a 1-rank NCCL communicator): same
+    fields as the plain batch call, the second step starts from the first step's deltaTChem (reference .C:130,398,490),
+    and the LoadBalancedTDAC driver leaves deltaTChem untouched (reference TDAC .C:968-971)."""
     import torch
-    from loadbalancedchemistrymodel_b200.model import CudaCellSolver, LoadBalancedChemistryModel
+    from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel
     sel = np.argsort(-flame["T"])[:512]
     Y, T, p, rho = _state(gri, flame, sel)
     opts = capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1)
     chem = capi.Chemistry(gri, opts, device=0)
     dev = torch.device("cuda", 0)
+    torch.cuda.set_device(0)
     tY, tT, tp, trho = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (Y, T, p, rho))
-    model = LoadBalancedChemistryModel(gri.n_species, CudaCellSolver(chem), dev)
+    model = LoadBalancedChemistryModel(chem)
     dtc0 = torch.full((sel.size,), DTCHEM, dtype=torch.float64, device=dev)
     m1 = model.solve(tY, tT, tp, trho, DT, dtc0)
     direct = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
@@ -215,6 +257,16 @@ def test_driver_on_one_gpu_equals_direct_call(gri, flame):
     m2 = model.solve(tY, tT, tp, trho, DT)                      # carries deltaTChem
     direct2 = chem.solve_host(Y, T, p, rho, DT, direct["deltaTChem"])
     assert np.array_equal(model.RR.cpu().numpy(), direct2["RR"])
+    # host-array entry point of the same step
+    ho = {"RR": np.empty_like(Y), "T": np.empty_like(T), "cost": np.empty_like(T), "status": np.empty(T.size, np.int32),
+          "deltaTChem": np.empty_like(T)}
+    m3 = model.solve_host(Y, T, p, rho, DT, direct["deltaTChem"], ho)
+    assert np.array_equal(ho["RR"], direct2["RR"]) and np.array_equal(ho["deltaTChem"], direct2["deltaTChem"]) and m3 == m2
+    model.close()
+    tdac = LoadBalancedChemistryModel(chem, tdac=True)
+    m4 = tdac.solve(tY, tT, tp, trho, DT, dtc0)
+    assert np.array_equal(tdac.RR.cpu().numpy(), direct["RR"]) and torch.equal(tdac.deltaTChem, dtc0) and m4 == DTCHEM
+    tdac.close()
     chem.close()
 
 
@@ -365,3 +417,187 @@ def test_tc_kernel(gri, flame):
     print(f"tc: min {got.min():.3e} s max {got.max():.3e} s, max rel err vs oracle {err.max():.2e}")
     assert (got > 0).all() and err.max() < 1e-9
     chem.close()
+
+
+# ---- option switches, host pipeline, cost order, device cellsToSend, the load-balanced step on real kernels ----------
+@pytest.mark.parametrize("solver,rel_tol", [("seulex", 1e-1), ("Rosenbrock34", 1e-2)])
+@pytest.mark.parametrize("switch", [dict(dfdx_is_dcdt=0), dict(kc_floor=1e-12), dict(gas_constant=8314.47),
+                                    dict(seulex_errold_max=1)])
+def test_doubtful_openfoam_details_are_switches_on_both_sides(gri, flame, solver, rel_tol, switch):
+    """Every OpenFOAM detail SURVEY Appendix A marks doubtful (dfdx = dcdt quirk, Kc floor, gas constant, seulex errOld)
+    is an option of the kernel AND of the oracle: parity with the non-default branch, on every 8th fixture cell."""
+    if "seulex_errold_max" in switch and solver != "seulex":
+        pytest.skip("seulex only")
+    sel = np.arange(0, flame["T"].shape[0], 8)
+    Y, T, p, rho = _state(gri, flame, sel)
+    opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, **switch)
+    if "gas_constant" in switch:
+        rho = rho * capi.RR_DEFAULT / 8314.47
+    got, ref, st = _solve_both(gri, Y, T, p, rho, opts)
+    _compare(gri, Y, rho, got, ref, DT, f"switch {switch}/{solver}", max_other_count=0.02)
+    base, _, _ = _solve_both(gri, Y, T, p, rho, capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol))
+    changed = not np.array_equal(base["RR"], got["RR"])
+    print("switch", switch, "changes the result:", changed)
+    if "kc_floor" not in switch:
+        assert changed                      # the switch reaches the kernel
+
+
+def test_seulex_tight_tolerance_uses_the_full_extrapolation_table(gri, flame):
+    """relTol 1e-8 starts seulex at kTarg = 5 and lets it climb: the kernel keeps the reference's full 11-row table
+    (no order cap), parity with the oracle at the same tolerance."""
+    sel = np.argsort(-flame["T"])[::29][:96]
+    Y, T, p, rho = _state(gri, flame, sel)
+    opts = capi.default_options(solver="seulex", abs_tol=1e-14, rel_tol=1e-8)
+    got, ref, st = _solve_both(gri, Y, T, p, rho, opts, dt=1e-5)
+    assert (got["status"] == 0).all()
+    _compare(gri, Y, rho, got, ref, 1e-5, "seulex 1e-8", abs_tol=1e-14, max_other_count=0.05)
+
+
+def test_host_pipeline_with_pinned_buffers_equals_device_path(gri, flame, monkeypatch):
+    """lbchem_solve_batch_host with PINNED caller arrays and many chunks: the kernels of consecutive chunks overlap on the
+    device (three streams), each with its own work queue and its own scratch; the result must be bit-identical to one
+    launch over device-resident arrays."""
+    import torch
+    monkeypatch.setenv("LBCHEM_CHUNK", "1024")
+    rep = 12
+    sel = np.tile(np.argsort(-flame["T"])[:1500], rep)
+    Y, T, p, rho = _state(gri, flame, sel)
+    n = sel.size
+    opts = capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1)
+    chem = capi.Chemistry(gri, opts)
+    pin = lambda a: torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+    out = {"RR": pin(np.empty((gri.n_species, n))), "T": pin(np.empty(n)), "cost": pin(np.empty(n)),
+           "status": pin(np.empty(n, np.int32)), "deltaTChem": pin(np.empty(n))}
+    for _ in range(3):
+        got = chem.solve_host(pin(Y), pin(T), pin(p), pin(rho), DT, DTCHEM, out=out)
+        dev = torch.device("cuda:0")
+        tY, tT, tp, trho = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (Y, T, p, rho))
+        dtc = torch.full((n,), DTCHEM, dtype=torch.float64, device=dev)
+        RR = torch.empty((gri.n_species, n), dtype=torch.float64, device=dev)
+        To = torch.empty(n, dtype=torch.float64, device=dev); co = torch.empty(n, dtype=torch.float64, device=dev)
+        so = torch.empty(n, dtype=torch.int32, device=dev)
+        chem.solve_device(n, n, tY, tT, tp, trho, DT, dtc, RR, To, co, so)
+        torch.cuda.synchronize()
+        assert np.array_equal(got["RR"], RR.cpu().numpy()) and np.array_equal(got["deltaTChem"], dtc.cpu().numpy())
+        assert np.array_equal(got["T"], To.cpu().numpy()) and np.array_equal(got["cost"], co.cpu().numpy())
+    chem.close()
+
+
+def test_cost_ordered_dispatch_gives_the_same_results(gri, flame):
+    """sort_by_cost: the work queue hands the cells out in descending order of the previous step's cost. Any order gives
+    bit-identical results; the order itself is a permutation sorted by cost."""
+    import torch
+    rng = np.random.default_rng(5)
+    sel = rng.permutation(flame["T"].shape[0])[:3000]
+    Y, T, p, rho = _state(gri, flame, sel)
+    n = sel.size
+    dev = torch.device("cuda:0")
+    tY, tT, tp, trho = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (Y, T, p, rho))
+    res = []
+    for sort in (0, 1):
+        chem = capi.Chemistry(gri, capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1, sort_by_cost=sort))
+        dtc = torch.full((n,), DTCHEM, dtype=torch.float64, device=dev)
+        RR = torch.empty((gri.n_species, n), dtype=torch.float64, device=dev)
+        To = torch.empty(n, dtype=torch.float64, device=dev); co = torch.zeros(n, dtype=torch.float64, device=dev)
+        so = torch.empty(n, dtype=torch.int32, device=dev)
+        for step in range(2):                            # the second step is dispatched by the first step's cost
+            chem.solve_device(n, n, tY, tT, tp, trho, DT, dtc, RR, To, co, so)
+        torch.cuda.synchronize()
+        res.append((RR.cpu().numpy(), dtc.cpu().numpy(), co.cpu().numpy()))
+        chem.close()
+    for a, b in zip(*res):
+        assert np.array_equal(a, b)
+
+
+def test_cells_to_send_on_the_device_is_bit_exact_at_full_size(gri):
+    """lbchem_cells_to_send_device (what lbchem_lb_solve runs) against the sequential host loop on 1 M integer costs with
+    fractional targets, chained bounds, targets of zero, unreachable targets, ragged sizes."""
+    import torch
+    chem = capi.Chemistry(gri, capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1))
+    rng = np.random.default_rng(9)
+    for n in (1, 5, 1023, 1024, 1025, 4000, 1_000_003):
+        cost = rng.integers(0, 90, n).astype(np.float64)
+        if n > 10:
+            cost[: n // 10] += rng.integers(50, 5000, n // 10)     # hot head
+        total = cost.sum()
+        tc = torch.from_numpy(cost).cuda()
+        for targets in ([total * 0.37], [total * 0.1234567, total * 0.25, 0.0, total * 0.031], [total * 2.0, 1.0], [0.5, 0.5, 1e-3],
+                        [total / 7.0] * 7):
+            want = [0]
+            for t in targets:
+                want.append(capi.cells_to_send(cost, t, want[-1]))
+            assert chem.cells_to_send_device(tc, targets) == want, (n, targets)
+    chem.close()
+
+
+@pytest.mark.parametrize("tdac", [False, True])
+def test_two_ranks_on_one_gpu_redistribute_real_cells(gri, flame, tdac):
+    """The load-balanced flow step (C++ driver, lbchem_lb_core.hpp) with the REAL CUDA solver: two logical ranks on the one
+    test GPU through the in-process loopback transport (device-to-device copies standing in for ncclSend / ncclRecv).
+    Rank 0 holds the flame (hot, expensive cells), rank 1 cold inflow cells: from the second step on rank 0 ships cells, and
+    every field must be bit-identical to the non-balanced solve of the same cells (the reference's own acceptance
+    criterion LB == non-LB, tests/src/standardChemistryModel-Test.C:90-102, here to the last bit)."""
+    import threading
+    import torch
+    from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel
+    order = np.argsort(-flame["T"])
+    sels = [order[:1500], order[-2000:]]
+    dev = torch.device("cuda:0")
+    opts = capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1, cost_model=1)
+    init = [list(gri.species).index(s) for s in DAC_INIT]
+    chems = [capi.Chemistry(gri, opts, device=0) for _ in range(2)]
+    single = capi.Chemistry(gri, opts, device=0)
+    if tdac:
+        for c in chems + [single]:
+            c.set_reduction(DAC_TOL, init)
+    models = LoadBalancedChemistryModel.make_loopback(chems, tdac=tdac)
+    states = []
+    for sel in sels:
+        Y, T, p, rho = _state(gri, flame, sel)
+        states.append(tuple(torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (Y, T, p, rho)) + ((Y, T, p, rho),))
+    dtc = [torch.full((sel.size,), DTCHEM, dtype=torch.float64, device=dev) for sel in sels]
+    ref_dtc = [np.full(sel.size, DTCHEM) for sel in sels]
+    errors = []
+    for step in range(3):
+        mins = [None, None]
+
+        def work(r):
+            try:
+                torch.cuda.set_device(0)
+                with torch.cuda.stream(torch.cuda.Stream(dev)):
+                    tY, tT, tp, trho, _ = states[r]
+                    mins[r] = models[r].solve(tY, tT, tp, trho, DT, dtc[r])
+                    torch.cuda.current_stream().synchronize()
+            except Exception as e:          # pragma: no cover
+                errors.append(e)
+        th = [threading.Thread(target=work, args=(r,)) for r in range(2)]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join(timeout=600)
+        assert not errors, errors
+        sent = [m.last["sent_cells"] for m in models]; recv = [m.last["recv_cells"] for m in models]
+        print(f"step {step}: sent {sent} recv {recv} plan {models[0].send_plan} total cost {[m.total_cost for m in models]}")
+        if step == 0:
+            assert sent == [0, 0] and not models[0].last["exchanged"]           # firstTime_: all local
+        else:
+            assert sent[0] > 0 and sent[0] == recv[1] and sent[1] == 0 and recv[0] == 0
+            assert models[0].send_plan and models[0].send_plan[0][0] == 1 and models[1].recv_plan == [0]
+        for r in range(2):
+            _, _, _, _, (Y, T, p, rho) = states[r]
+            want = single.solve_host(Y, T, p, rho, DT, ref_dtc[r])
+            m = models[r]
+            assert np.array_equal(m.RR.cpu().numpy(), want["RR"]), (step, r)
+            assert np.array_equal(m.T_out.cpu().numpy(), want["T"]) and np.array_equal(m.cell_cost.cpu().numpy(), want["cost"])
+            assert np.array_equal(m.status.cpu().numpy(), want["status"])
+            if tdac:      # LoadBalancedTDAC never copies deltaTChem back (reference TDAC .C:968-971)
+                assert np.array_equal(m.deltaTChem.cpu().numpy(), ref_dtc[r]) and mins[r] == DTCHEM
+            else:
+                assert np.array_equal(m.deltaTChem.cpu().numpy(), want["deltaTChem"]) and mins[r] == want["deltaTChem"].min()
+                ref_dtc[r] = want["deltaTChem"]
+                dtc[r] = m.deltaTChem
+            assert m.total_cost == want["cost"].sum()
+    for m in models:
+        m.close()
+    for c in chems + [single]:
+        c.close()
