@@ -209,7 +209,43 @@ class Ranks:
 IMB = {"solver": "seulex", "absTol": 1e-12, "relTol": 1e-3, "deltaT": 1e-4}
 
 
-def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north_star"):
+def cpu_plan_baseline(ranks, cells_per_rank):
+    """The reference's own path on the host cores for the imbalanced batch: `ranks` MPI-like sub-domains (one oracle thread
+    each, static contiguous partition) integrate a bounded sample of the same workload, per-cell wall clock recorded as
+    the reference does (LoadBalancedChemistryModel.C:431-448); then the reference's plan (updateProcessorBalancing +
+    cellsToSend on those per-cell times) is applied and the makespan of the re-distributed work is evaluated from the
+    measured per-cell times. Returns cells/s without and with the plan."""
+    from loadbalancedchemistrymodel_b200 import capi
+    from loadbalancedchemistrymodel_b200 import workloads as W
+    from oracle import oracle as O
+    parts = [W.gri_skewed(cells_per_rank, rank=r, world=ranks) for r in range(ranks)]
+    mech = parts[0][0]
+    Y = np.ascontiguousarray(np.concatenate([q[1] for q in parts], axis=1))
+    T, p, rho = (np.concatenate([q[k] for q in parts]) for k in (2, 3, 4))
+    om = O.OracleModel(mech, capi.default_options(solver=IMB["solver"], abs_tol=IMB["absTol"], rel_tol=IMB["relTol"]))
+    r1 = om.solve_batch(Y, T, p, rho, IMB["deltaT"], 1e-7, nthreads=ranks)               # firstTime_ step
+    t0 = time.perf_counter()
+    r2 = om.solve_batch(Y, T, p, rho, IMB["deltaT"], r1["deltaTChem"], nthreads=ranks)   # carried sub-step guess, timed
+    wall = time.perf_counter() - t0
+    ct = r2["cpu_time"].reshape(ranks, cells_per_rank)
+    load = ct.sum(1)
+    send, recv = capi.balance_plan(load, np.full(ranks, cells_per_rank, np.int32), 0.02)
+    after = load.copy()
+    for r in range(ranks):
+        start = 0
+        for to, frac in send[r]:
+            end = capi.cells_to_send(ct[r], load[r] * frac, start)
+            moved = ct[r, start:end].sum()
+            after[r] -= moved; after[to] += moved
+            start = end
+    n = ranks * cells_per_rank
+    return {"ranks": ranks, "sample_cells": n, "wall_s_unbalanced": wall, "cells_per_s_unbalanced": n / load.max(),
+            "cells_per_s_with_reference_plan": n / after.max(), "rank_load_s": [float(x) for x in load],
+            "rank_load_s_after_plan": [float(x) for x in after],
+            "how": "oracle threads as MPI ranks; plan applied to the measured per-cell wall times (makespan = slowest rank)"}
+
+
+def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north_star", cpu_plan=False):
     """The load-balancing experiment: `total_cells` in TOTAL (strong scaling), the hot 10 % contiguous at the start of the
     global index space (rank 0 holds them), deltaTChem carried from step to step, integrated once without and once
     with the redistribution (same lbchem_lb entry point, balance off / on). seulex 1e-12 / 1e-3 over deltaT = 1e-4 is the
@@ -245,7 +281,7 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
         out = {"RR": torch.empty((nSp, n), dtype=torch.float64, device=dev), "T": torch.empty(n, dtype=torch.float64, device=dev),
                "cost": torch.empty(n, dtype=torch.float64, device=dev), "status": torch.empty(n, dtype=torch.int32, device=dev)}
         dtc = dtc0
-        nwarm = 1 if mode == "unbalanced" else 2          # step 0 is local in both; the balanced model plans on step 1
+        nwarm = 2                                          # step 0 is local in both; the balanced model plans on step 1
         times, moved, nbytes, kms = [], 0, 0, []
         for it in range(nwarm + steps):
             R.barrier()
@@ -303,6 +339,9 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
         c2.close()
         h, c = float(r2["cost"][:ns].mean()), float(r2["cost"][ns:].mean())
         split = {"attempts_hot_cell": h, "attempts_cold_cell": c, "hot_10pct_share_of_attempts": 0.1 * h / (0.1 * h + 0.9 * c)}
+    if cpu_plan and rank == 0 and not dac:
+        cores = os.cpu_count() or 1
+        rec["cpu_reference_plan"] = cpu_plan_baseline(cores, 96)
     rec.update({
         "ms_per_step_unbalanced": ub["ms"], "ms_per_step_balanced": bl["ms"], "speedup_from_balancing": ub["ms"] / bl["ms"],
         "cells_per_s_balanced": n * world / (bl["ms"] * 1e-3), "cells_per_s_unbalanced": n * world / (ub["ms"] * 1e-3),
@@ -448,7 +487,8 @@ def run_b200(args):
     if not args.no_imbalanced and args.workload == "gri_uniform":
         if model is not None:
             model.close(); model = None
-        imbalanced = run_imbalanced(R, rank, local, args.imbalanced_cells, steps=args.imbalanced_steps)
+        imbalanced = run_imbalanced(R, rank, local, args.imbalanced_cells, steps=args.imbalanced_steps,
+                                    cpu_plan=(world == 1 and not args.no_cpu_baseline))
         if world == 8 and not args.no_extra_configs:
             extra["config4_gri_skewed_4M"] = run_imbalanced(R, rank, local, 4_000_000, steps=1, label="BASELINE config 4")
             extra["config5_gri_dac_1M"] = run_imbalanced(R, rank, local, 1_000_000, dac=True, steps=3, label="BASELINE config 5")

@@ -112,8 +112,8 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oPIV, oXCH, oXS, oCNT, oA, oMSK;
-    const unsigned long long* jterm; const int* jthrEnt; const int* jthrN;
+    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA, oMSK, oSX;
+    const unsigned* jterm; const unsigned long long* dterm; int nD; const int* jthrEnt; const int* jthrN;
     const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
@@ -128,10 +128,11 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
     c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
     c.oRD = p; p += N;
-    c.oBS = p; p += N; c.oPIV = p; p += (N + 1) / 2;
+    c.oBS = p; p += N;
+    c.oSX = p; p += 24;                       // seulex: temp[12], dxOpt[12] (group-uniform step-size bookkeeping)
     c.oSTEP = p; p += (N + 1) / 2;
     c.lda = (M.nSp + 1) | 1;                  // odd (GRI: 55): one column read across the 16 rows of a half-warp touches 16 distinct 8-byte banks
-    c.oA = p; p += (M.nSp * c.lda > 2 * M.nR) ? M.nSp * c.lda : 2 * M.nR;   // KF/KR alias the matrix
+    c.oA = p; p += (M.nSp * c.lda > 2 * M.nR + M.nD) ? M.nSp * c.lda : 2 * M.nR + M.nD;   // KF/KR and the Jacobian's D terms alias the matrix
     return (p + 1) & ~1;
 }
 #define WS(name) (base + cx->o##name)
@@ -358,32 +359,43 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
             const double d0 = (t < nSp && (cx->O.dfdxIsDcdt || dydt0)) ? gather_species(S, WS(OM), t) : 0.0;
             if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? d0 : 0.0;
             if (dydt0) finish_derivatives(g, cx, base, T, d0, dydt0);
-            // gather program: acc += coef * k * c1 * c2 * c3, entry closed by the `last` flag
+            // (1) D terms: k * product of the other concentrations, one per (reaction, side, species), into the matrix
+            //     region behind KF/KR; each is shared by every Jacobian row its reaction touches
             const double* KFR = WS(A); const double* CC = WS(CC); double* JS = GS_JS;
-            const int nR = S.nR;
+            const int nR = S.nR, nD = cx->nD;
+            double* D = WS(A) + 2 * nR;
+            {
+                const unsigned long long* dp = cx->dterm;
+#pragma unroll 4
+                for (int k = t; k < nD; k += TPC) {
+                    const unsigned long long wd = dp[k];
+                    const unsigned kid = V2_T_K(wd);
+                    const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
+                    D[k] = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
+                }
+            }
+            g.sync();
+            // (2) entry gather program: acc += coef * D[term], entry closed by the `last` flag. The program streams from
+            //     global memory (L2): eight words are fetched ahead so that one round trip is paid per eight terms
             const int nT = cx->jthrN[t];
             int e = cx->jthrEnt[t];
             double acc = 0.0;
-            const unsigned long long* prog = cx->jterm + t;
-            // the program streams from global memory (L2): fetch eight words ahead so that one L2 round trip is paid per
-            // eight terms instead of per term
+            const unsigned* prog = cx->jterm + t;
             constexpr int PF = 8;
-            unsigned long long cur[PF], nxt[PF];
+            unsigned cur[PF];
 #pragma unroll
-            for (int q = 0; q < PF; ++q) cur[q] = (q < nT) ? prog[(size_t)q * TPC] : 0ull;
+            for (int q = 0; q < PF; ++q) cur[q] = prog[(size_t)q * TPC];          // padded by PF rows on the host
 #pragma unroll 1
             for (int k0 = 0; k0 < nT; k0 += PF) {
+                unsigned nxt[PF];
 #pragma unroll
-                for (int q = 0; q < PF; ++q) nxt[q] = (k0 + PF + q < nT) ? prog[(size_t)(k0 + PF + q) * TPC] : 0ull;
+                for (int q = 0; q < PF; ++q) nxt[q] = prog[(size_t)(k0 + PF + q) * TPC];
 #pragma unroll
                 for (int q = 0; q < PF; ++q) {
                     if (k0 + q < nT) {
-                        const unsigned long long wd = cur[q];
-                        const unsigned kid = V2_T_K(wd);
-                        const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
-                        const double d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
-                        acc = fma((double)V2_T_COEF(wd), d, acc);
-                        if (V2_T_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
+                        const unsigned wd = cur[q];
+                        acc = fma((double)V2_J_COEF(wd), D[V2_J_D(wd)], acc);
+                        if (V2_J_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
                     }
                 }
 #pragma unroll
@@ -437,7 +449,6 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     double* A = WS(A);
     double* RD = WS(RD);
     int* STEP = reinterpret_cast<int*>(WS(STEP));
-    int* PIV = reinterpret_cast<int*>(WS(PIV));   // PIV[j] = row that became the pivot row of column j
     double* XCH = WS(XCH);
     double* row = A + t * lda;
     g.sync();
@@ -470,7 +481,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const unsigned long long act = DAC ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(S.nR + 63) >> 6] : ~0ull;
     bool done = (t >= nSp) || !((act >> t) & 1ull);
     int pos = t;
-    if (done && t < N) { STEP[t] = t; PIV[t] = t; RD[t] = 1.0 / dg; }
+    if (done && t < N) { STEP[t] = t; RD[t] = 1.0 / dg; }
     int par = 1;      // exchange buffer, toggled per pivot column (with DAC two consecutive pivot columns may share j & 1)
 #pragma unroll 1
     for (ColsUp cu(DAC, act, nSp); cu.next<DAC>();) {
@@ -479,13 +490,18 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
         const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        // one reduction on the top 32 bits of the key decides the warp's candidate whenever that maximum is unique
+        // (the common case); ties in the top half fall through to the exact 64-bit + position comparison
         const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
         const bool c1 = hi == mh;
-        const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
-        const bool c2 = c1 && lo == ml;
-        const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
-        const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
-        const bool win = c2 && pp == mp;
+        bool win = c1;
+        if (__popc(__ballot_sync(0xffffffffu, c1)) != 1) {
+            const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
+            const bool c2 = c1 && lo == ml;
+            const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
+            const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
+            win = c2 && pp == mp;
+        }
         if (win) {
             double* slot = XCH + (g.warp * 2 + par) * 4;
             slot[0] = __longlong_as_double((long long)key);
@@ -504,7 +520,7 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const int ptid = reinterpret_cast<const int*>(sw + 1)[1];
         const double rd = sw[2];
         if (t == ptid) {
-            done = true; STEP[t] = j; PIV[j] = t; RD[j] = rd;
+            done = true; STEP[t] = j; RD[j] = rd;
             if (piv == 0.0) row[j] = LB_SMALL;
         } else if (!done) {
             if (pos == j) pos = ppos;
@@ -886,13 +902,14 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
     const double absTol = O.absTol, relTol = O.relTol;
     const double jacRedo = fmin(1e-4, relTol);
     double *y = VEC(0), *y0 = VEC(4), *scale = VEC(5), *ySeq = VEC(6), *tb = GS_TB;
-    double temp[12], dxOpt[12];
-    temp[0] = LB_GREAT;
+    // temp / dxOpt are group-uniform: one copy in the workspace (every thread writes the same value; reads follow a group
+    // barrier of the column loop), not 48 registers per thread
+    double* temp = WS(SX); double* dxOpt = temp + 12;
     double dx = step.dxTry;
     g.sync();
     if (t < N) { y0[t] = y[t]; scale[t] = absTol + relTol * fabs(y[t]); }
     cs.f0valid = 0;
-    dxOpt[0] = fabs(0.1 * dx);
+    temp[0] = LB_GREAT; dxOpt[0] = fabs(0.1 * dx);
     if (step.first || step.prevReject) cs.theta = 2.0 * jacRedo;
     if (step.first) {
         const double logTol = -log10(relTol + absTol) * 0.6 + 0.5;
@@ -1076,7 +1093,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
         cxw->O = O; cxw->O.solver = SOLVER;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
-        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = M.dac;
+        cxw->jterm = M.jterm; cxw->dterm = M.dterm; cxw->nD = M.nD; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = M.dac;
         cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
     }
     __syncthreads();
@@ -1189,7 +1206,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, 
         cxw->O = O;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
-        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
+        cxw->jterm = M.jterm; cxw->dterm = M.dterm; cxw->nD = M.nD; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
         cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
     }
     __syncthreads();
@@ -1247,7 +1264,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) probe_v3_kernel(V2Mech M, DevOpts 
         cxw->O = O;
         cxw->nEqn = M.nEqn; cxw->nEnt = M.nEnt; cxw->nFall = M.nFall; cxw->tbRows = M.tbRows;
         cxw->wsDoubles = ctx_layout(*cxw, M);
-        cxw->jterm = M.jterm; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
+        cxw->jterm = M.jterm; cxw->dterm = M.dterm; cxw->nD = M.nD; cxw->jthrEnt = M.jthrEnt; cxw->jthrN = M.jthrN; cxw->dac = nullptr;
         cxw->scratch = B.scratch; cxw->scratchStride = B.scratchStride; cxw->groups = blockDim.x / TPC;
     }
     __syncthreads();

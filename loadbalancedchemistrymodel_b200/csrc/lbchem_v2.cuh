@@ -38,8 +38,10 @@ struct V2Mech {
     int oSpPtr, oSpList;
     int oRowPtr, oEntCol;
     const unsigned char* blob;           // global copy of the blob
-    // Jacobian gather program (global, thread-interleaved: term k of thread t at [k*64 + t])
-    const unsigned long long* jterm;
+    // Jacobian: D-term program [nD] (k index and the three concentration factors of d omega / d c), then the entry gather
+    // program (global, thread-interleaved: term k of thread t at [k*64 + t]; 32-bit words: D index, coefficient, last flag)
+    const unsigned long long* dterm; int nD;
+    const unsigned* jterm;
     const int* jthrEnt;                  // [65] first entry of thread t
     const int* jthrN;                    // [64] number of terms of thread t
     int jMaxTerms;
@@ -48,12 +50,12 @@ struct V2Mech {
     int wsDoubles;                       // per-cell workspace in doubles
 };
 
-// Jacobian gather term (64 bits):
-//   [0,16) index into KFR (2*pos + side)   [16,24) [24,32) [32,40) species factors (nSp = the constant 1)
-//   [40,48) signed coefficient (-/+ nu * e_j)   bit 48: last term of its entry
+// D term (64 bits): [0,16) index into KFR (2*pos + side)   [16,24) [24,32) [32,40) species factors (nSp = the constant 1)
 #define V2_T_K(w) ((unsigned)((w) & 0xffffull))
 #define V2_T_S1(w) ((unsigned)(((w) >> 16) & 0xffull))
 #define V2_T_S2(w) ((unsigned)(((w) >> 24) & 0xffull))
 #define V2_T_S3(w) ((unsigned)(((w) >> 32) & 0xffull))
-#define V2_T_COEF(w) ((int)(signed char)(((w) >> 40) & 0xffull))
-#define V2_T_LAST(w) ((unsigned)(((w) >> 48) & 1ull))
+// Jacobian gather term (32 bits): [0,12) D-term index   [12,20) signed coefficient (-/+ nu * e_j)   bit 20: last term of its entry
+#define V2_J_D(w) ((w) & 0xfffu)
+#define V2_J_COEF(w) ((int)(signed char)(((w) >> 12) & 0xffu))
+#define V2_J_LAST(w) (((w) >> 20) & 1u)

@@ -248,8 +248,11 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         M.oSpPtr = B.add(spPtr); M.oSpList = B.add(spList);
     }
 
-    // Jacobian entries (row, col) -> gather terms in the reference's accumulation order
-    struct Term { int kidx, s[3]; int coef; };
+    // Jacobian: (1) "D terms" d(omega_r)/d(c_col) / nu = k * prod of the other concentrations, one per (reaction, side,
+    // species j of that side) -- each is shared by every row the reaction touches; (2) entries (row, col) -> sums of
+    // coef * D[term] in the reference's accumulation order (reactions ascending, forward side before reverse side).
+    struct Term { int didx; int coef; };
+    std::vector<unsigned long long> dterm;                 // D-term program: kidx | s1 << 16 | s2 << 24 | s3 << 32
     std::map<std::pair<int, int>, std::vector<Term>> E;
     for (int r = 0; r < nR; ++r) {
         for (int side = 0; side < 2; ++side) {
@@ -259,12 +262,15 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
             if (side == 1 && !m->reversible[r]) continue;      // kr == 0: contributes exact zeros
             const int b = ptr[r], e = ptr[r + 1];
             for (int j = b; j < e; ++j) {
-                Term t; t.kidx = 2 * posOf[r] + side; int nf = 0;
+                int sp3[3]; int nf = 0;
                 for (int i = b; i < e; ++i) {
                     const int reps = (int)ex[i] - (i == j ? 1 : 0);
-                    for (int q = 0; q < reps; ++q) { if (nf >= 3) return 1; t.s[nf++] = spc[i]; }
+                    for (int q = 0; q < reps; ++q) { if (nf >= 3) return 1; sp3[nf++] = spc[i]; }
                 }
-                while (nf < 3) t.s[nf++] = nSp;                // CC[nSp] == 1.0
+                while (nf < 3) sp3[nf++] = nSp;                // CC[nSp] == 1.0
+                Term t; t.didx = (int)dterm.size();
+                dterm.push_back((unsigned long long)(2 * posOf[r] + side) | ((unsigned long long)sp3[0] << 16) |
+                                ((unsigned long long)sp3[1] << 24) | ((unsigned long long)sp3[2] << 32));
                 const int ej = (int)ex[j];
                 const int col = spc[j];
                 // d(omega)/dc_col = +kf-term for side 0, -kr-term for side 1; species on the lhs lose, rhs gain
@@ -279,6 +285,8 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
             }
         }
     }
+    if (dterm.size() > 4095) return 1;
+    M.nD = (int)dterm.size();
     // irreversible reactions still own the (row, col) entries of their rhs columns in the oracle (zeros); they
     // only matter structurally, and a structural zero equals an absent entry for the LU build.
     const int nEnt = (int)E.size();
@@ -307,7 +315,7 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     M.oEntCol = B.add(entCol);
 
     // deal entries to `tpc` threads in contiguous runs balanced by term count; program word k of thread t at [k*tpc + t]
-    struct Prog { std::vector<unsigned long long> jterm; std::vector<int> thrEnt, thrN; int maxT; };
+    struct Prog { std::vector<unsigned> jterm; std::vector<int> thrEnt, thrN; int maxT; };
     auto deal = [&](int tpc) {
         Prog P;
         std::vector<int> thrEnt(tpc + 1, nEnt), thrN(tpc, 0);
@@ -320,16 +328,15 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
             }
             while (t + 1 <= tpc) thrEnt[++t] = nEnt;
         }
-        std::vector<std::vector<unsigned long long>> perThr(tpc);
+        std::vector<std::vector<unsigned>> perThr(tpc);
         {
             int e = 0;
             for (auto& kv : E) {
                 int t = 0; while (!(e >= thrEnt[t] && e < thrEnt[t + 1])) ++t;
                 for (size_t q = 0; q < kv.second.size(); ++q) {
                     const Term& u = kv.second[q];
-                    unsigned long long w = (unsigned long long)u.kidx | ((unsigned long long)u.s[0] << 16) | ((unsigned long long)u.s[1] << 24) |
-                                           ((unsigned long long)u.s[2] << 32) | ((unsigned long long)(uint8_t)(int8_t)u.coef << 40);
-                    if (q + 1 == kv.second.size()) w |= 1ull << 48;
+                    unsigned w = (unsigned)u.didx | ((unsigned)(uint8_t)(int8_t)u.coef << 12);
+                    if (q + 1 == kv.second.size()) w |= 1u << 20;
                     perThr[t].push_back(w);
                 }
                 ++e;
@@ -337,7 +344,7 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         }
         int maxT = 1;
         for (int t = 0; t < tpc; ++t) { thrN[t] = (int)perThr[t].size(); maxT = std::max(maxT, thrN[t]); }
-        std::vector<unsigned long long> jterm((size_t)maxT * tpc, 0ull);
+        std::vector<unsigned> jterm((size_t)(maxT + 16) * tpc, 0u);   // + 16 rows: the kernel reads eight words ahead of a batch of eight
         for (int t = 0; t < tpc; ++t)
             for (int k = 0; k < thrN[t]; ++k) jterm[(size_t)k * tpc + t] = perThr[t][k];
 
@@ -356,14 +363,16 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         *dst = d;
         return true;
     };
-    const void *dBlob, *dTerm, *dEnt, *dN;
-    if (!up(B.b.data(), B.b.size(), &dBlob) || !up(P64.jterm.data(), P64.jterm.size() * 8, &dTerm) ||
+    const void *dBlob, *dTerm, *dEnt, *dN, *dD;
+    for (int q = 0; q < 8 * V2_TPC; ++q) dterm.push_back(0ull);          // read-ahead padding
+    if (!up(B.b.data(), B.b.size(), &dBlob) || !up(P64.jterm.data(), P64.jterm.size() * 4, &dTerm) || !up(dterm.data(), dterm.size() * 8, &dD) ||
         !up(P64.thrEnt.data(), P64.thrEnt.size() * 4, &dEnt) || !up(P64.thrN.data(), P64.thrN.size() * 4, &dN)) {
         err = "cudaMalloc/cudaMemcpy failed while uploading the packed mechanism";
         return LBCHEM_E_CUDA;
     }
     M.blob = static_cast<const unsigned char*>(dBlob);
-    M.jterm = static_cast<const unsigned long long*>(dTerm);
+    M.jterm = static_cast<const unsigned*>(dTerm);
+    M.dterm = static_cast<const unsigned long long*>(dD);
     M.jthrEnt = static_cast<const int*>(dEnt);
     M.jthrN = static_cast<const int*>(dN);
     *out = M;

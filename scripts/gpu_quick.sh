@@ -1,9 +1,11 @@
 #!/bin/bash
-# quick GPU iteration: parity tests + one small bench per solver. usage: gpurun -- 'bash scripts/gpu_quick.sh TAG [cells]'
-TAG=${1:-q}; CELLS=${2:-200000}; OUT=gpurun_out; mkdir -p $OUT
-timeout 900 python -m pytest tests -m gpu -x -q > $OUT/${TAG}_pytest.log 2>&1; echo "pytest exit $?"; tail -3 $OUT/${TAG}_pytest.log
-for S in seulex Rosenbrock34; do
-  LBCHEM_VERBOSE=1 timeout 600 python bench.py --cells $CELLS --steps 2 --warmup 3 --no-e2e --no-cpu-baseline --solver $S > $OUT/${TAG}_bench_$S.json 2> $OUT/${TAG}_bench_$S.err; echo "bench $S exit $?"
-  grep -m1 "lbchem\] v3" $OUT/${TAG}_bench_$S.err
-  python -c "import json;d=json.load(open('$OUT/${TAG}_bench_$S.json'));print('$S',d['value'],d['roofline']['frac'],d['failed_cells'])" || tail -5 $OUT/${TAG}_bench_$S.err
+# quick A/B: 200 k cells, both solvers, device-resident value only; tag = $1
+mkdir -p gpurun_out
+for s in seulex Rosenbrock34; do
+  python bench.py --cells 200000 --steps 3 --warmup 3 --solver $s --no-e2e --no-cpu-baseline --no-imbalanced > gpurun_out/q_${1}_$s.json 2> gpurun_out/q_${1}_$s.err
+  python - <<PY
+import json
+d=json.load(open("gpurun_out/q_${1}_$s.json"))
+print("${1}", "$s", round(d["value"]), "cells/s  frac", round(d["roofline"]["frac"],4), "failed", d["failed_cells"])
+PY
 done
