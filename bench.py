@@ -31,8 +31,12 @@ ROOT = Path(__file__).resolve().parent
 sys.path.insert(0, str(ROOT))
 
 METRIC = "cell-chemistry solves/s (GRI-3.0, 1 flow step)"
+CPU_SCALE = {"h2_air": 20, "ch4_mixing": 200}      # cells of the CPU sample relative to GRI: the small mechanisms are that much cheaper per cell
+METRIC_OF = {"h2_air": "cell-chemistry solves/s (H2/O2, 1 flow step)", "ch4_mixing": "cell-chemistry solves/s (1-step CH4, 1 flow step)"}
 UNIT = "cells/s"
-SOLVERS = {"seulex": ("seulex", 1e-12, 1e-1), "Rosenbrock34": ("Rosenbrock34", 1e-12, 1e-2)}
+SOLVERS = {"seulex": ("seulex", 1e-12, 1e-1), "Rosenbrock34": ("Rosenbrock34", 1e-12, 1e-2),
+           "EulerImplicit": ("EulerImplicit", 1e-12, 1e-2)}     # EulerImplicitCoeffs{cTauChem 1; equilibriumRateLimiter off}
+MECH_OF = {"h2_air": "H2/O2 sub-mechanism of GRI-3.0 (10 species, 29 reactions)", "ch4_mixing": "1-step CH4 (5 species, 1 reaction)"}
 
 
 def parse():
@@ -43,7 +47,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", type=int, default=1_000_000, help="cells per GPU")
     ap.add_argument("--solver", default="seulex", choices=list(SOLVERS))
-    ap.add_argument("--workload", default="gri_uniform", choices=["gri_uniform", "gri_skewed", "gri_dac", "gri_tiled"])
+    ap.add_argument("--workload", default="gri_uniform", choices=["gri_uniform", "gri_skewed", "gri_dac", "gri_tiled", "h2_air", "ch4_mixing"])
     ap.add_argument("--cpu-sample", type=int, default=0, help="cells in the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -63,6 +67,10 @@ def make_workload(name, n, rank, world=1):
         return W.gri_skewed(n, rank=rank, world=world)
     if name in ("gri_dac", "gri_tiled"):
         return W.gri_tiled(n, rank=rank)
+    if name == "h2_air":
+        return W.h2_air(n, rank=rank)
+    if name == "ch4_mixing":
+        return W.ch4_mixing_line(n, rank=rank)
     return W.gri_uniform(n, rank=rank)
 
 
@@ -77,6 +85,8 @@ WORKLOAD_TEXT = {
     "gri_uniform": "BASELINE config 3; fixture cells T>1500 K resampled + noise, seed 1003",
     "gri_skewed": "BASELINE config 4; hot cells (T>1500 K) contiguous at the start of the global index space, cold cells T<350 K, seed 1004",
     "gri_tiled": "BASELINE config 5 input without the reduction: the unfiltered 4000-cell fixture tiled + noise, seed 1005",
+    "h2_air": "BASELINE config 2; H2/air, phi ~ U(0.5, 2), T ~ U(900, 2500) K, p = 1e5, radical seed, seed 1002",
+    "ch4_mixing": "BASELINE config 1 input; CH4 / air mixing line, z ~ U(0, 1), T ~ U(293, 2000) K, seed 1001",
     "gri_dac": "BASELINE config 5; the unfiltered 4000-cell fixture tiled + noise, seed 1005; reduction{active on; method DAC; "
                "tolerance 1e-4; initialSet CO CH4 HO2}, tabulation off",
 }
@@ -85,9 +95,9 @@ WORKLOAD_TEXT = {
 def config_dict(args, n_gpus, extra=None):
     s, atol, rtol = SOLVERS[args.solver]
     cfg = {
-        "workload": f"{args.workload}: GRI-Mech 3.0 (53 species, 325 reactions), {args.cells} synthetic cells per GPU "
+        "workload": f"{args.workload}: {MECH_OF.get(args.workload, 'GRI-Mech 3.0 (53 species, 325 reactions)')}, {args.cells} synthetic cells per GPU "
                     f"({WORKLOAD_TEXT[args.workload]})",
-        "mechanism": "GRI-3.0", "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
+        "mechanism": MECH_OF.get(args.workload, "GRI-3.0"), "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
         "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; every step through lbchem_lb_solve (C++ driver: all-gather of the cost, bit-exact plan, device cellsToSend, NCCL p2p of field-major row slices, one two-segment launch)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
         "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
     }
@@ -121,11 +131,11 @@ def run_reference(args):
     if rank != 0:
         return
     cores = os.cpu_count() or 1
-    n_sample = args.cpu_sample or min(args.cells, 1500 * cores)
+    n_sample = args.cpu_sample or min(args.cells, 1500 * cores * CPU_SCALE.get(args.workload, 1))
     rate, dt, _ = cpu_oracle_rate(args, n_sample, cores, steps=args.steps, warmup=args.warmup)
     sample = f"{n_sample} cells of the workload per step, {cores} threads, static contiguous partition"
     line = {
-        "impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": METRIC_OF.get(args.workload, METRIC), "value": rate, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic", "config": config_dict(args, args.gpus),
         "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
@@ -505,7 +515,8 @@ def run_b200(args):
         except Exception:
             pass
         hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-        hbm_ach = 912.0 * st["n_cells"] / (k_ms * 1e-3) / 1e9
+        cell_bytes = (2 * nSp + 8) * 8                                  # (nSp + 5) doubles in, (nSp + 3) out: 912 B for GRI
+        hbm_ach = cell_bytes * st["n_cells"] / (k_ms * 1e-3) / 1e9
         traffic, traffic_src = None, None   # dram bytes per launch from the committed ncu --set full capture of this kernel
         try:
             tr = json.loads((ROOT / "profiles" / "r02_traffic.json").read_text())
@@ -517,22 +528,23 @@ def run_b200(args):
         roofline = {
             "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
             "traffic_source": traffic_src,
-            "kernel": "v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)", "kernel_ms": k_ms,
+            "kernel": ("v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)" if nSp + 2 > 16 and s != "EulerImplicit"
+                       else "integrate_kernel<8 or 16 threads per cell> (general kernel, sub-warp groups; lbchem_kernels.cu)"), "kernel_ms": k_ms,
             "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
             "flops_per_cell": flops / max(1, st["n_cells"]), "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts"
                           + (" at the FULL system size n = 55 (upper bound: the reduced systems are smaller)" if args.workload == "gri_dac" else ""),
             "hbm": {"achieved": hbm_ach, "peak": hbm_peak, "unit": "GB/s", "frac": hbm_ach / hbm_peak,
-                    "bytes_per_cell": 912, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
+                    "bytes_per_cell": cell_bytes, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback"},
         }
         cpu = None
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            n_sample = args.cpu_sample or min(n, 600 * cores)
+            n_sample = args.cpu_sample or min(n, 600 * cores * CPU_SCALE.get(args.workload, 1))
             rate, dtc_s, _ = cpu_oracle_rate(args, n_sample, cores, steps=1, warmup=1)
             cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
                    "sample": f"{n_sample} cells of the same workload, second of two passes, {cores} threads ({dtc_s:.1f} s)"}
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+            "metric": METRIC_OF.get(args.workload, METRIC), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic", "config": config_dict(args, world), "clocks": clocks, "e2e": e2e,
             "gpu_launches": gpu_launches, "roofline": roofline, "cpu_baseline": cpu,

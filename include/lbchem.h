@@ -114,7 +114,8 @@ typedef struct lbchem_options {
     int32_t dfdx_is_dcdt;         /* 1 = OpenFOAM quirk: jacobian() leaves dcdt in the dfdx slot */
     double gas_constant;          /* RR, J/(kmol K); default 8314.47 (OpenFOAM thermodynamicConstants) */
     double kc_floor;              /* kr = kf / max(Kc, kc_floor); default 1e-6 */
-    int32_t threads_per_cell;     /* 0 = choose from mechanism size; else 32/64/128 */
+    int32_t threads_per_cell;     /* 0 = choose kernel and group width from the mechanism size; 8/16/32/64 = general kernel
+                                     with that many threads per cell (8 and 16: several cells share one warp) */
     int32_t sort_by_cost;         /* 1 = lbchem_solve_batch dispatches cells to the work queue in descending order of the
                                      cost[] array as it holds on ENTRY (the previous flow step's per-cell cost) */
     int32_t seulex_errold_max;    /* seulex: errOld = max(4 err, 1) [1, Numerical Recipes] or min(4 err, 1) [0, default]:

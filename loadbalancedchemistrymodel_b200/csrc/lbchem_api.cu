@@ -185,6 +185,12 @@ int configure_v2(lbchem_handle h) {
     const lbchem_options& o = h->opts;
     if (!h->v2Built || o.threads_per_cell != 0 || getenv("LBCHEM_GENERAL_KERNEL")) return LBCHEM_OK;
     if (o.solver != LBCHEM_SOLVER_SEULEX && o.solver != LBCHEM_SOLVER_ROSENBROCK34) return LBCHEM_OK;
+    // small mechanisms (H2/O2: 12 equations, 1-step CH4: 7) run on the general kernel with 8 / 16 threads per cell: a
+    // 64-thread group would leave most lanes idle and only six cells resident per SM (LBCHEM_SMALL_KERNEL=v3 overrides)
+    {
+        const char* sk = getenv("LBCHEM_SMALL_KERNEL");
+        if (h->M.nEqn <= 16 && !(sk && !strcmp(sk, "v3"))) return LBCHEM_OK;
+    }
     if (lb_v3_supported(h->V2)) {
         const int ws = lb_v3_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol);
         const size_t per3 = (size_t)ws * sizeof(double);
@@ -219,8 +225,11 @@ int configure(lbchem_handle h) {
         if (rc != LBCHEM_OK) return rc;
     }
     int tpc = h->opts.threads_per_cell;
-    if (tpc == 0) tpc = (h->M.nEqn <= 32) ? 32 : 64;
-    if (tpc != 32 && tpc != 64) return fail(h, LBCHEM_E_INVALID, "threads_per_cell must be 0, 32 or 64");
+    if (tpc == 0) {
+        tpc = h->M.nEqn <= 8 ? 8 : (h->M.nEqn <= 16 ? 16 : (h->M.nEqn <= 32 ? 32 : 64));
+        if (const char* e = getenv("LBCHEM_TPC")) if (atoi(e) > 0) tpc = atoi(e);
+    }
+    if (tpc != 8 && tpc != 16 && tpc != 32 && tpc != 64) return fail(h, LBCHEM_E_INVALID, "threads_per_cell must be 0, 8, 16, 32 or 64");
     if (h->configuredSolver == h->opts.solver && h->configuredTpc == tpc) return LBCHEM_OK;
     if (h->configuredTpc != tpc) {
         int rc = build_jacobian_lists(h, tpc);
@@ -230,7 +239,7 @@ int configure(lbchem_handle h) {
     h->wsDoubles = lb_work_doubles(h->M, h->opts.solver);
     const size_t per = h->wsDoubles * sizeof(double);
     if (per > h->smemMax) return fail(h, LBCHEM_E_UNSUPPORTED, "mechanism too large for one cell's shared-memory workspace");
-    int groups = (int)std::min<size_t>(8, h->smemMax / per);
+    int groups = (int)std::min<size_t>(tpc < 32 ? 16 : 8, h->smemMax / per);
     const char* env = getenv("LBCHEM_GROUPS");
     if (env && atoi(env) > 0) groups = std::min(groups, atoi(env));
     h->groups = groups;

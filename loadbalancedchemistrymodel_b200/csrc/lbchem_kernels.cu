@@ -23,15 +23,18 @@ struct Grp {
     int gid;        // group index inside the CTA
     double* red;    // 2 slots x 2 warps of reduction scratch (shared)
     int tog;
+    unsigned mask;  // lanes of this group inside its warp (TPC < 32: several cells share one warp, each an independent
+                    // sub-warp group that only ever synchronises and shuffles inside its own lanes)
 
+    static constexpr int kHalf = TPC < 32 ? TPC / 2 : 16;
     __device__ __forceinline__ void sync() const {
-        if (TPC == 32) __syncwarp();
+        if (TPC <= 32) __syncwarp(mask);
         else asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory");
     }
     __device__ __forceinline__ double sum(double v) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (TPC == 32) return v;
+        for (int o = kHalf; o > 0; o >>= 1) v += __shfl_xor_sync(mask, v, o);
+        if (TPC <= 32) return v;
         double* r = red + 4 * tog; tog ^= 1;
         if ((tid & 31) == 0) r[tid >> 5] = v;
         sync();
@@ -42,8 +45,8 @@ struct Grp {
     }
     __device__ __forceinline__ double max(double v) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o));
-        if (TPC == 32) return v;
+        for (int o = kHalf; o > 0; o >>= 1) v = fmax(v, __shfl_xor_sync(mask, v, o));
+        if (TPC <= 32) return v;
         double* r = red + 4 * tog; tog ^= 1;
         if ((tid & 31) == 0) r[tid >> 5] = v;
         sync();
@@ -60,8 +63,8 @@ struct Grp {
         return b > 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : m;
     }
     __device__ __forceinline__ int any(int p) {
-        int a = __any_sync(0xffffffffu, p);
-        if (TPC == 32) return a;
+        int a = __any_sync(mask, p);
+        if (TPC <= 32) return a;
         double* r = red + 4 * tog; tog ^= 1;
         if ((tid & 31) == 0) r[tid >> 5] = a ? 1.0 : 0.0;
         sync();
@@ -73,12 +76,12 @@ struct Grp {
     // lexicographic arg-max of (key, idx); ties on key go to the larger idx (LUDecompose's ">=" scan)
     __device__ __forceinline__ int argmax(unsigned long long key, int idx) {
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            unsigned long long k2 = __shfl_xor_sync(0xffffffffu, key, o);
-            int i2 = __shfl_xor_sync(0xffffffffu, idx, o);
+        for (int o = kHalf; o > 0; o >>= 1) {
+            unsigned long long k2 = __shfl_xor_sync(mask, key, o);
+            int i2 = __shfl_xor_sync(mask, idx, o);
             if (k2 > key || (k2 == key && i2 > idx)) { key = k2; idx = i2; }
         }
-        if (TPC == 32) return idx;
+        if (TPC <= 32) return idx;
         double* r = red + 4 * tog; tog ^= 1;
         if ((tid & 31) == 0) {
             r[tid >> 5] = __longlong_as_double((long long)key);
@@ -491,7 +494,7 @@ template <int TPC>
 __device__ void lu_solve(Grp<TPC>& g, const DevMech& M, Work& w, const double* A, int n, double* b) {
     const int lda = M.lda;
     g.sync();
-    if (n <= 64) {
+    if (TPC >= 32 && n <= 64) {
         if (g.tid < 32) {
             const int lane = g.tid, i0 = lane, i1 = lane + 32;
             double b0 = i0 < n ? b[w.perm[i0]] : 0.0;
@@ -965,12 +968,13 @@ __device__ __forceinline__ void carve(Work& w, Grp<TPC>& g, double* base, const 
 }
 
 template <int TPC>
-__global__ void __launch_bounds__(TPC * 8) integrate_kernel(DevMech M, DevOpts O, BatchArgs B, int groups, int wsDoubles) {
+__global__ void __launch_bounds__(TPC * (TPC < 32 ? 16 : 8)) integrate_kernel(DevMech M, DevOpts O, BatchArgs B, int groups, int wsDoubles) {
     extern __shared__ double smem[];
     Grp<TPC> g;
     g.tid = threadIdx.x % TPC;
     g.gid = threadIdx.x / TPC;
     g.tog = 0;
+    g.mask = TPC >= 32 ? 0xffffffffu : (((1u << (TPC & 31)) - 1u) << ((threadIdx.x & 31) & ~(TPC - 1)));
     Work w;
     carve(w, g, smem + (size_t)g.gid * wsDoubles, M, O.solver);
     const int nSp = M.nSp;
@@ -979,7 +983,7 @@ __global__ void __launch_bounds__(TPC * 8) integrate_kernel(DevMech M, DevOpts O
     for (;;) {
         unsigned long long q = 0;
         if (g.tid == 0) q = atomicAdd(B.queue, 1ull);
-        q = __shfl_sync(0xffffffffu, q, 0);
+        q = __shfl_sync(g.mask, q, TPC >= 32 ? 0 : ((threadIdx.x & 31) & ~(TPC - 1)));
         if (TPC > 32) {
             // broadcast across the group's warps through shared memory
             g.sync();
@@ -1057,7 +1061,7 @@ __global__ void __launch_bounds__(TPC * 8) integrate_kernel(DevMech M, DevOpts O
 //   LUSOLVE in: A[nEqn*nEqn], b[nEqn]   out: x[nEqn]
 //   RATES   in: y[nEqn]                 out: kf[nR], kr[nR]
 template <int TPC>
-__global__ void __launch_bounds__(TPC * 8) probe_kernel(DevMech M, DevOpts O, int kind, int nItems, const double* in, double* out,
+__global__ void __launch_bounds__(TPC * (TPC < 32 ? 16 : 8)) probe_kernel(DevMech M, DevOpts O, int kind, int nItems, const double* in, double* out,
                                                          int inStride, int outStride, int wsDoubles) {
     extern __shared__ double smem[];
     Grp<TPC> g;
@@ -1117,20 +1121,33 @@ static cudaError_t configure(int groups, size_t smemBytes, int* ctasPerSM) {
 }
 
 cudaError_t lb_configure(int tpc, int groups, size_t smemBytes, int* ctasPerSM) {
-    return tpc == 32 ? configure<32>(groups, smemBytes, ctasPerSM) : configure<64>(groups, smemBytes, ctasPerSM);
+    switch (tpc) {
+        case 8: return configure<8>(groups, smemBytes, ctasPerSM);
+        case 16: return configure<16>(groups, smemBytes, ctasPerSM);
+        case 32: return configure<32>(groups, smemBytes, ctasPerSM);
+        default: return configure<64>(groups, smemBytes, ctasPerSM);
+    }
 }
 
 cudaError_t lb_launch_integrate(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const DevMech& M,
                                 const DevOpts& O, const BatchArgs& B, cudaStream_t s) {
-    if (tpc == 32) integrate_kernel<32><<<grid, groups * 32, smemBytes, s>>>(M, O, B, groups, wsDoubles);
-    else integrate_kernel<64><<<grid, groups * 64, smemBytes, s>>>(M, O, B, groups, wsDoubles);
+    switch (tpc) {
+        case 8: integrate_kernel<8><<<grid, groups * 8, smemBytes, s>>>(M, O, B, groups, wsDoubles); break;
+        case 16: integrate_kernel<16><<<grid, groups * 16, smemBytes, s>>>(M, O, B, groups, wsDoubles); break;
+        case 32: integrate_kernel<32><<<grid, groups * 32, smemBytes, s>>>(M, O, B, groups, wsDoubles); break;
+        default: integrate_kernel<64><<<grid, groups * 64, smemBytes, s>>>(M, O, B, groups, wsDoubles);
+    }
     return cudaGetLastError();
 }
 
 cudaError_t lb_launch_probe(int tpc, int groups, size_t smemBytes, int wsDoubles, const DevMech& M, const DevOpts& O,
                             int kind, int nItems, const double* in, double* out, int inStride, int outStride, cudaStream_t s) {
     const int grid = (nItems + groups - 1) / groups;
-    if (tpc == 32) probe_kernel<32><<<grid, groups * 32, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles);
-    else probe_kernel<64><<<grid, groups * 64, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles);
+    switch (tpc) {
+        case 8: probe_kernel<8><<<grid, groups * 8, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles); break;
+        case 16: probe_kernel<16><<<grid, groups * 16, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles); break;
+        case 32: probe_kernel<32><<<grid, groups * 32, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles); break;
+        default: probe_kernel<64><<<grid, groups * 64, smemBytes, s>>>(M, O, kind, nItems, in, out, inStride, outStride, wsDoubles);
+    }
     return cudaGetLastError();
 }

@@ -543,7 +543,7 @@ def test_two_ranks_on_one_gpu_redistribute_real_cells(gri, flame, tdac):
     import torch
     from loadbalancedchemistrymodel_b200.model import LoadBalancedChemistryModel
     order = np.argsort(-flame["T"])
-    sels = [order[:1500], order[-2000:]]
+    sels = [order[:2500], order[-700:]]          # rank 0: 2500 flame cells, rank 1: 700 cold inflow cells
     dev = torch.device("cuda:0")
     opts = capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1, cost_model=1)
     init = [list(gri.species).index(s) for s in DAC_INIT]
