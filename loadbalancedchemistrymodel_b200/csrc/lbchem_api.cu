@@ -185,18 +185,18 @@ int configure_v2(lbchem_handle h) {
     const lbchem_options& o = h->opts;
     if (!h->v2Built || o.threads_per_cell != 0 || getenv("LBCHEM_GENERAL_KERNEL")) return LBCHEM_OK;
     if (o.solver != LBCHEM_SOLVER_SEULEX && o.solver != LBCHEM_SOLVER_ROSENBROCK34) return LBCHEM_OK;
-    // small mechanisms (H2/O2: 12 equations, 1-step CH4: 7) run on the general kernel with 8 / 16 threads per cell: a
-    // 64-thread group would leave most lanes idle and only six cells resident per SM (LBCHEM_SMALL_KERNEL=v3 overrides)
+    // small mechanisms (H2/O2: 12 equations, 1-step CH4: 7) run the same compact-code kernel with 16 / 8 threads per cell
+    // (LBCHEM_SMALL_KERNEL=general selects the general kernel with sub-warp groups instead, for A/B runs)
     {
         const char* sk = getenv("LBCHEM_SMALL_KERNEL");
-        if (h->M.nEqn <= 16 && !(sk && !strcmp(sk, "v3"))) return LBCHEM_OK;
+        if (sk && !strcmp(sk, "general") && h->M.nEqn <= 16) return LBCHEM_OK;
     }
     if (lb_v3_supported(h->V2)) {
         const int ws = lb_v3_workspace(h->V2, o.solver, o.rel_tol, o.abs_tol);
         const size_t per3 = (size_t)ws * sizeof(double);
         const size_t fixed = (size_t)lb_v3_ctx_bytes() + h->V2.hotBytes;
         if (fixed + per3 <= h->smemMax) {
-            int groups = (int)std::min<size_t>(6, (h->smemMax - fixed) / per3);
+            int groups = (int)std::min<size_t>(lb_v3_max_groups(h->V2.tpc), (h->smemMax - fixed) / per3);
             if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
             h->v3Groups = groups; h->v3Ws = ws;
             h->scratchStride = (h->V2.nEnt + 11 * h->V2.nEqn + 1) & ~1;
@@ -208,10 +208,10 @@ int configure_v2(lbchem_handle h) {
                 h->scratchCap = need;
             }
             h->v3Smem = fixed + per3 * groups;
-            CK(lb_v3_configure(o.solver, h->v3Smem));
+            CK(lb_v3_configure(h->V2.tpc, o.solver, h->v3Smem));
             if (getenv("LBCHEM_VERBOSE"))
-                fprintf(stderr, "[lbchem] v3 kernel: %d cells per CTA, %d B workspace per cell, %d B mechanism in smem, %zu B dynamic smem\n",
-                        groups, (int)per3, h->V2.hotBytes, h->v3Smem);
+                fprintf(stderr, "[lbchem] v3 kernel: %d threads per cell, %d cells per CTA, %d B workspace per cell, %d B mechanism in smem, %zu B dynamic smem\n",
+                        h->V2.tpc, groups, (int)per3, h->V2.hotBytes, h->v3Smem);
             h->useV3 = true;
             return LBCHEM_OK;
         }
@@ -383,7 +383,7 @@ int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int3
     if (!h) return LBCHEM_E_INVALID;
     CK(cudaSetDevice(h->device));
     if (!active) { h->dacOn = false; h->V2.dac = nullptr; return LBCHEM_OK; }
-    if (h->dacProg.empty() || !h->v2Built)
+    if (h->dacProg.empty() || !h->v2Built || h->V2.tpc != 64)
         return fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction needs the packed mechanism of the compact-code kernel (nSp <= 62, integer stoichiometry)");
     if (!(tolerance > 0.0) || n_init < 1 || n_init > 8 || !init_species)
         return fail(h, LBCHEM_E_INVALID, "reduction: tolerance must be > 0 and the initial set must hold 1..8 species");
@@ -435,7 +435,7 @@ int lbchem_tc(lbchem_handle h, int64_t n, int64_t ldy, const double* Y, const do
     long long grid = h->nSM;
     const long long need = (n + h->v3Groups - 1) / h->v3Groups;
     if (grid > need) grid = need;
-    CK(lb_v3_tc((int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, tc, static_cast<cudaStream_t>(stream)));
+    CK(lb_v3_tc(h->V2.tpc, (int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, tc, static_cast<cudaStream_t>(stream)));
     return LBCHEM_OK;
 }
 
@@ -477,7 +477,7 @@ int lb_launch_batch(lbchem_handle h, const CellSeg* a, const CellSeg* b, double 
         long long grid3 = h->nSM;
         const long long need3 = (n + h->v3Groups - 1) / h->v3Groups;
         if (grid3 > need3) grid3 = need3;
-        CK(lb_v3_launch(h->opts.solver, (int)grid3, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, s));
+        CK(lb_v3_launch(h->V2.tpc, h->opts.solver, (int)grid3, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, s));
         h->launches++;
         return LBCHEM_OK;
     }
@@ -672,7 +672,7 @@ int lbchem_probe(lbchem_handle h, int32_t kind, int32_t nItems, const double* in
         long long grid = h->nSM;
         const long long need = (nItems + h->v3Groups - 1) / h->v3Groups;
         if (grid > need) grid = need;
-        CK(lb_v3_probe((int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, kind, nItems, dIn, inStride, dOut, outStride, 0));
+        CK(lb_v3_probe(h->V2.tpc, (int)grid, h->v3Groups, h->v3Smem, h->v3Ws, h->V2, h->O, B, kind, nItems, dIn, inStride, dOut, outStride, 0));
     } else {
         CK(lb_launch_probe(h->tpc, h->groups, h->smemBytes, (int)h->wsDoubles, h->M, h->O, kind, nItems, dIn, dOut, inStride, outStride, 0));
     }

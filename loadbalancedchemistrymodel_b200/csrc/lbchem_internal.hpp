@@ -10,17 +10,18 @@
 #include "lbchem_v2.cuh"
 
 int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allocs, std::string& err, std::vector<int>* posOfOut);
-cudaError_t lb_v3_probe(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+cudaError_t lb_v3_probe(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
                         int kind, int nItems, const double* in, int inStride, double* out, int outStride, cudaStream_t s);
-cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+cudaError_t lb_v3_tc(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
                      double* tcOut, cudaStream_t s);
 cudaError_t lb_launch_qdot(long long n, long long ldy, int nSp, const double* hf, const double* RR, double* Qdot, cudaStream_t s);
 int lb_dac_program(const lbchem_mech_desc* m, double tol, int nInit, const int32_t* init, std::vector<int>& prog, int* nPairsOut);
 int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol);
 bool lb_v3_supported(const V2Mech& M);
 int lb_v3_ctx_bytes();
-cudaError_t lb_v3_configure(int solver, size_t smemBytes);
-cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
+cudaError_t lb_v3_configure(int tpc, int solver, size_t smemBytes);
+int lb_v3_max_groups(int tpc);
+cudaError_t lb_v3_launch(int tpc, int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s);
 size_t lb_work_doubles(const DevMech& M, int solver);
 cudaError_t lb_configure(int tpc, int groups, size_t smemBytes, int* ctasPerSM);

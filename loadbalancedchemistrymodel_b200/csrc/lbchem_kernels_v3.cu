@@ -21,7 +21,6 @@
 
 namespace v3 {
 
-constexpr int TPC = 64;
 
 struct SMech {            // typed views into the staged blob
     int nSp, nR, nEff;
@@ -56,56 +55,6 @@ __device__ __forceinline__ void bind_cold(SMech& S, const V2Mech& M) {
 #undef PC
 }
 
-// Group-level helpers. Threads derive their coordinates from threadIdx; nothing lives in local memory, so the
-// heavy routines below can be real (non-inlined) functions with exactly one copy in the instruction stream.
-struct Grp {
-    int tid, gid, lane, warp;
-    double* red;      // 32 doubles of exchange scratch at the start of the group's workspace: 4 slots of 8
-    __device__ __forceinline__ Grp(double* base) {
-        tid = threadIdx.x % TPC; gid = threadIdx.x / TPC; lane = threadIdx.x & 31; warp = tid >> 5; red = base;
-    }
-    __device__ __forceinline__ void sync() const { asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory"); }
-    // Reductions write slot `s` (0..3). Two reductions with no barrier in between must use different slots.
-    __device__ __forceinline__ void sum3(double& a, double& b, double& c, int s) const {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            a += __shfl_xor_sync(0xffffffffu, a, o); b += __shfl_xor_sync(0xffffffffu, b, o); c += __shfl_xor_sync(0xffffffffu, c, o);
-        }
-        double* r = red + 8 * s;
-        if (lane == 0) { r[warp * 3] = a; r[warp * 3 + 1] = b; r[warp * 3 + 2] = c; }
-        sync();
-        a = r[0] + r[3]; b = r[1] + r[4]; c = r[2] + r[5];
-    }
-    __device__ __forceinline__ double sum(double a, int s) const {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
-        double* r = red + 8 * s;
-        if (lane == 0) r[warp] = a;
-        sync();
-        return r[0] + r[1];
-    }
-    __device__ __forceinline__ double maxnan(double v, int s) const {   // max with NaN propagation
-        double bad = (v != v) ? 1.0 : 0.0;
-        v = (v != v) ? 0.0 : v;
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) {
-            v = fmax(v, __shfl_xor_sync(0xffffffffu, v, o)); bad = fmax(bad, __shfl_xor_sync(0xffffffffu, bad, o));
-        }
-        double* r = red + 8 * s;
-        if (lane == 0) { r[warp * 2] = v; r[warp * 2 + 1] = bad; }
-        sync();
-        v = fmax(r[0], r[2]); bad = fmax(r[1], r[3]);
-        return bad > 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : v;
-    }
-    __device__ __forceinline__ int any(int p, int s) const {
-        const int a = __any_sync(0xffffffffu, p);
-        double* r = red + 8 * s;
-        if (lane == 0) r[warp] = a ? 1.0 : 0.0;
-        sync();
-        return (r[0] + r[1]) > 0.0;
-    }
-};
-
 // Per-CTA context in shared memory: mechanism views, options and the layout of a group's workspace
 // (offsets in doubles from the group's base). Every routine takes (cx, base).
 struct Ctx {
@@ -130,7 +79,7 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oRD = p; p += N;
     c.oBS = p; p += N;
     c.oSX = p; p += 24;                       // seulex: temp[12], dxOpt[12] (group-uniform step-size bookkeeping)
-    c.oSTEP = p; p += (N + 1) / 2;
+    c.oSTEP = p; p += N + 1;                  // int STEP[N] (pivot column of each row), then int SPOF[N] (DAC: species of a compact column)
     c.lda = (M.nSp + 1) | 1;                  // odd (GRI: 55): one column read across the 16 rows of a half-warp touches 16 distinct 8-byte banks
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR + M.nD) ? M.nSp * c.lda : 2 * M.nR + M.nD;   // KF/KR and the Jacobian's D terms alias the matrix
     return (p + 1) & ~1;
@@ -163,9 +112,97 @@ __device__ __forceinline__ double side_product(const double* c, unsigned long lo
     return f;
 }
 
+
+struct Cell { int fail; double theta; int kTarg; int f0valid; };
+struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
+
+__constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
+__constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434, 625};
+
+// smem layout: [Ctx (padded to 512 B)] [mechanism blob] [groups x workspace]
+constexpr int CTX_BYTES = 512;
+static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
+
+// threads per CTA: 384 whatever the group width (register file: 168 registers per thread)
+template <int TPC> struct Width { static constexpr int kMaxGroups = 384 / TPC; };
+
+// ================================================================================================
+// Everything below is written once for a group of TPC threads integrating one cell: TPC = 64 (two warps, named
+// barriers; GRI-class mechanisms up to 62 species), 32, 16 or 8 (sub-warp groups: several cells share one warp, each
+// group synchronises and shuffles only inside its own lanes; H2/O2 with 12 equations runs 24 cells per SM on 16 lanes
+// each, the 1-step CH4 mechanism 48 cells on 8 lanes each). Thread t of a group owns species row t, so TPC >= nEqn.
+// ================================================================================================
+template <int TPC>
+struct K {
+
+// Group-level helpers. Threads derive their coordinates from threadIdx; nothing lives in local memory, so the
+// heavy routines below can be real (non-inlined) functions with exactly one copy in the instruction stream.
+struct Grp {
+    int tid, gid, lane, warp;
+    unsigned mask;    // lanes of this group inside its warp (all of them when TPC >= 32)
+    double* red;      // 32 doubles of exchange scratch at the start of the group's workspace: 4 slots of 8
+    static constexpr int kHalf = TPC < 32 ? TPC / 2 : 16;
+    static constexpr bool kTwoWarps = TPC > 32;
+    __device__ __forceinline__ Grp(double* base) {
+        tid = threadIdx.x % TPC; gid = threadIdx.x / TPC; lane = threadIdx.x & 31; warp = tid >> 5; red = base;
+        mask = TPC >= 32 ? 0xffffffffu : (((1u << (TPC & 31)) - 1u) << (lane & ~(TPC - 1)));
+    }
+    // group barrier (also orders the group's shared and global memory accesses): a named barrier for two warps, a
+    // (sub-)warp barrier otherwise
+    __device__ __forceinline__ void sync() const {
+        if (kTwoWarps) asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory");
+        else __syncwarp(mask);
+    }
+    // Reductions write slot `s` (0..3). Two reductions with no barrier in between must use different slots. Every
+    // reduction ends with a group barrier (callers rely on it to publish what they wrote before the call).
+    __device__ __forceinline__ void sum3(double& a, double& b, double& c, int s) const {
+#pragma unroll
+        for (int o = kHalf; o > 0; o >>= 1) {
+            a += __shfl_xor_sync(mask, a, o); b += __shfl_xor_sync(mask, b, o); c += __shfl_xor_sync(mask, c, o);
+        }
+        if (!kTwoWarps) { sync(); return; }
+        double* r = red + 8 * s;
+        if (lane == 0) { r[warp * 3] = a; r[warp * 3 + 1] = b; r[warp * 3 + 2] = c; }
+        sync();
+        a = r[0] + r[3]; b = r[1] + r[4]; c = r[2] + r[5];
+    }
+    __device__ __forceinline__ double sum(double a, int s) const {
+#pragma unroll
+        for (int o = kHalf; o > 0; o >>= 1) a += __shfl_xor_sync(mask, a, o);
+        if (!kTwoWarps) { sync(); return a; }
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a;
+        sync();
+        return r[0] + r[1];
+    }
+    __device__ __forceinline__ double maxnan(double v, int s) const {   // max with NaN propagation
+        double bad = (v != v) ? 1.0 : 0.0;
+        v = (v != v) ? 0.0 : v;
+#pragma unroll
+        for (int o = kHalf; o > 0; o >>= 1) {
+            v = fmax(v, __shfl_xor_sync(mask, v, o)); bad = fmax(bad, __shfl_xor_sync(mask, bad, o));
+        }
+        if (kTwoWarps) {
+            double* r = red + 8 * s;
+            if (lane == 0) { r[warp * 2] = v; r[warp * 2 + 1] = bad; }
+            sync();
+            v = fmax(r[0], r[2]); bad = fmax(r[1], r[3]);
+        } else sync();
+        return bad > 0.0 ? __longlong_as_double(0x7ff8000000000000LL) : v;
+    }
+    __device__ __forceinline__ int any(int p, int s) const {
+        const int a = __any_sync(mask, p);
+        if (!kTwoWarps) { sync(); return a; }
+        double* r = red + 8 * s;
+        if (lane == 0) r[warp] = a ? 1.0 : 0.0;
+        sync();
+        return (r[0] + r[1]) > 0.0;
+    }
+};
+
 // clamp c, refresh Gibbs functions and third-body sums for temperature T; ends with a group sync.
 // y: state vector (c, T, p). If `clamp` is false CC is taken as current (finite-difference passes).
-__device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* base, const double* y, double T, double lnT, bool clamp) {
+static __device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* base, const double* y, double T, double lnT, bool clamp) {
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid;
     double* CC = WS(CC);
@@ -191,7 +228,7 @@ __device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, double* bas
 // omega of every reaction at (CC, T) into OM[pos]; keep != 0 also stores kf, kr (Jacobian assembly).
 // Pass structure (one exp call site): exponentials -> fall-off blending -> kf, kr, mass action.
 template <bool DAC>
-__device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int keep, double T, double lnT, double invT) {
+static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int keep, double T, double lnT, double invT) {
     const Grp g(base);
     const SMech& S = cx->S;
     const int nR = S.nR, nFall = cx->nFall;
@@ -280,7 +317,7 @@ __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, int kee
 // dc_i/dt = sum over the reactions of species i of nu * omega. Four interleaved partial sums (terms k, k+1, k+2, k+3
 // of the reference's order), combined as (a0 + a1) + (a2 + a3): the species with > 100 reactions (H, OH, O ...)
 // would otherwise serialise one ~30-cycle dependent FMA per term while the rest of the group waits at the barrier.
-__device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
+static __device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     const int e = S.spPtr[i + 1];
     int k = S.spPtr[i];
@@ -302,7 +339,7 @@ __device__ __forceinline__ double gather_species(const SMech& S, const double* o
 
 // tail of StandardChemistryModel::derivatives: dT/dt = -sum h_i w_i / (rho cp) from the species rates `d` (thread t owns
 // species t), CC and T current; writes dydt and counts one derivatives() evaluation
-__device__ __forceinline__ void finish_derivatives(const Grp& g, const Ctx* cx, double* base, double T, double d, double* dydt) {
+static __device__ __forceinline__ void finish_derivatives(const Grp& g, const Ctx* cx, double* base, double T, double d, double* dydt) {
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid;
     const double RR = cx->O.RR;
@@ -324,7 +361,7 @@ __device__ __forceinline__ void finish_derivatives(const Grp& g, const Ctx* cx, 
 
 // StandardChemistryModel::derivatives (A.8): y, dydt are vectors of the group's workspace
 template <bool DAC>
-__device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
+static __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const double* y, double* dydt) {
     const Grp g(base);
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid;
@@ -339,7 +376,7 @@ __device__ __noinline__ void derivatives(const Ctx* cx, double* base, const doub
 // StandardChemistryModel::jacobian (A.9) into the sparse store: JS[entry] (species block, structural
 // non-zeros in (row, col) order), JT[i] = d(dc_i/dt)/dT by central difference; dfdx = species rates (A.4 quirk)
 template <bool DAC>
-__device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx, double* dydt0) {
+static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double* y, double* dfdx, double* dydt0) {
     const Grp g(base);
     const SMech& S = cx->S;
     const int nSp = S.nSp, t = g.tid, N = cx->nEqn;
@@ -410,103 +447,117 @@ __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const double*
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_JAC]++;
 }
 
-// DAC: walk the columns of the kept species only. The 64-bit active word is held as two 32-bit halves: taking the lowest
-// (highest) remaining bit is one FLO + one logic op, where 64-bit shifts and find-first-set cost a dozen instructions per
-// column (15 % of the reduced kernel's instructions in the first version).
-struct ColsUp {
-    unsigned lo, hi; int j, nSp;
-    __device__ __forceinline__ ColsUp(bool dac, unsigned long long act, int n) : lo((unsigned)act), hi((unsigned)(act >> 32)), j(-1), nSp(n) { (void)dac; }
-    template <bool DAC> __device__ __forceinline__ bool next() {
-        if (!DAC) return ++j < nSp;
-        if (lo) { j = __ffs((int)lo) - 1; lo &= lo - 1u; return true; }
-        if (hi) { j = 31 + __ffs((int)hi); hi &= hi - 1u; return true; }
-        return false;
+// ------------------------------------------------------------------------------------------------
+// dense linear algebra on the shared-memory matrix: thread t owns the row of species t of  dg*I - J
+// (columns: species block + temperature column). The T and p rows are (0 .. dg .. 0): handled in closed form.
+//
+// DAC (LoadBalancedTDAC, reduction active): the kept species are COMPACTED -- species t sits in row / column
+// cm(t) = number of kept species below t, the matrix is NsDAC x (NsDAC + 1) with its own odd stride, and every loop runs
+// over NsDAC columns: this is TDACChemistryModel's reduced system (simplifiedToCompleteIndex_ is ascending, so the
+// compact order is the reference's order, which its pivot tie rule needs). Threads of removed species idle here; their
+// equations are decoupled (dc/dt = 0, diagonal dg).
+// ------------------------------------------------------------------------------------------------
+template <bool DAC>
+struct Compact {
+    unsigned long long act; int Ns, ldc;
+    __device__ __forceinline__ Compact(const Ctx* cx, const double* base) {
+        const int nSp = cx->S.nSp;
+        if (DAC) {
+            act = reinterpret_cast<const unsigned long long*>(base + cx->oMSK)[(cx->S.nR + 63) >> 6];
+            Ns = __popcll(act);
+            ldc = (Ns + 1) | 1;
+        } else { act = ~0ull; Ns = nSp; ldc = cx->lda; }
     }
-};
-struct ColsDown {
-    unsigned lo, hi; int j;
-    __device__ __forceinline__ ColsDown(unsigned long long act, int nSp) : lo((unsigned)act), hi((unsigned)(act >> 32)), j(nSp) {}
-    template <bool DAC> __device__ __forceinline__ bool next() {
-        if (!DAC) return --j >= 0;
-        if (hi) { const int b = 31 - __clz((int)hi); j = 32 + b; hi ^= 1u << b; return true; }
-        if (lo) { const int b = 31 - __clz((int)lo); j = b; lo ^= 1u << b; return true; }
-        return false;
-    }
+    __device__ __forceinline__ bool kept(int sp) const { return !DAC || ((act >> sp) & 1ull); }
+    __device__ __forceinline__ int index(int sp) const { return DAC ? __popcll(act & ((1ull << sp) - 1ull)) : sp; }
 };
 
-// ------------------------------------------------------------------------------------------------
-// dense linear algebra on the shared-memory matrix: thread t owns species row t of  dg*I - J
-// (columns 0..nSp: species block + temperature column). The T and p rows are (0 .. dg .. 0): handled in closed form.
-// ------------------------------------------------------------------------------------------------
 // Build the matrix from the sparse Jacobian and factorise it: LUDecompose (A.10) with implicit row scaling and
 // partial pivoting. Rows never move: `pos` is the index the row would have in the reference's physically swapped
 // matrix (drives its tie rule: the LAST maximal row wins), STEP[t] the column at which row t became the pivot row.
 template <bool DAC>
-__device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
+static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
     const Grp g(base);
     const SMech& S = cx->S;
-    const int nSp = S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
+    const int nSp = S.nSp, t = g.tid, N = cx->nEqn;
+    const Compact<DAC> cp(cx, base);
+    const int Ns = cp.Ns, ldc = cp.ldc;
+    const bool mine = t < nSp && cp.kept(t);
+    const int cm = mine ? cp.index(t) : 0;
     double* A = WS(A);
     double* RD = WS(RD);
     int* STEP = reinterpret_cast<int*>(WS(STEP));
+    int* SPOF = STEP + N + (N & 1);               // DAC: species of compact column j
     double* XCH = WS(XCH);
-    double* row = A + t * lda;
+    double* row = A + cm * ldc;
     g.sync();
     double big = fabs(dg);
-    if (t < nSp) {
+    if (mine) {
 #pragma unroll 1
-        for (int k = 0; k <= nSp; ++k) row[k] = 0.0;
+        for (int k = 0; k <= Ns; ++k) row[k] = 0.0;
         const double* JS = GS_JS;
         const int e1 = S.rowPtr[t + 1];
         // JS and the column list stream from global memory (L2): four independent loads per round trip
         int e = S.rowPtr[t];
+        if (!DAC) {
 #pragma unroll 1
-        for (; e + 3 < e1; e += 4) {
-            const int c0 = S.entCol[e], c1 = S.entCol[e + 1], c2 = S.entCol[e + 2], c3 = S.entCol[e + 3];
-            const double v0 = JS[e], v1 = JS[e + 1], v2 = JS[e + 2], v3 = JS[e + 3];
-            row[c0] = -v0; row[c1] = -v1; row[c2] = -v2; row[c3] = -v3;
+            for (; e + 3 < e1; e += 4) {
+                const int c0 = S.entCol[e], c1 = S.entCol[e + 1], c2 = S.entCol[e + 2], c3 = S.entCol[e + 3];
+                const double v0 = JS[e], v1 = JS[e + 1], v2 = JS[e + 2], v3 = JS[e + 3];
+                row[c0] = -v0; row[c1] = -v1; row[c2] = -v2; row[c3] = -v3;
+            }
+#pragma unroll 1
+            for (; e < e1; ++e) row[S.entCol[e]] = -JS[e];
+        } else {
+#pragma unroll 1
+            for (; e + 3 < e1; e += 4) {
+                const int c0 = S.entCol[e], c1 = S.entCol[e + 1], c2 = S.entCol[e + 2], c3 = S.entCol[e + 3];
+                const double v0 = JS[e], v1 = JS[e + 1], v2 = JS[e + 2], v3 = JS[e + 3];
+                if (cp.kept(c0)) row[cp.index(c0)] = -v0;
+                if (cp.kept(c1)) row[cp.index(c1)] = -v1;
+                if (cp.kept(c2)) row[cp.index(c2)] = -v2;
+                if (cp.kept(c3)) row[cp.index(c3)] = -v3;
+            }
+#pragma unroll 1
+            for (; e < e1; ++e) { const int c = S.entCol[e]; if (cp.kept(c)) row[cp.index(c)] = -JS[e]; }
+            SPOF[cm] = t;
         }
-#pragma unroll 1
-        for (; e < e1; ++e) row[S.entCol[e]] = -JS[e];
-        row[nSp] = -WS(JT)[t];
-        row[t] += dg;
+        row[Ns] = -WS(JT)[t];
+        row[cm] += dg;
         big = 0.0;
 #pragma unroll 1
-        for (int k = 0; k <= nSp; ++k) big = fmax(big, fabs(row[k]));
+        for (int k = 0; k <= Ns; ++k) big = fmax(big, fabs(row[k]));
     }
     if (g.any(t < N && big == 0.0, 2)) return LBCHEM_CELL_SINGULAR;
     const double vv = 1.0 / big;
-    // DAC: the rows and columns of removed species hold only the diagonal dg (no reaction touches them), i.e. the reduced
-    // system of the reference embedded in the full index space: such a row is its own pivot row and its column is skipped
-    const unsigned long long act = DAC ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(S.nR + 63) >> 6] : ~0ull;
-    bool done = (t >= nSp) || !((act >> t) & 1ull);
-    int pos = t;
-    if (done && t < N) { STEP[t] = t; RD[t] = 1.0 / dg; }
-    int par = 1;      // exchange buffer, toggled per pivot column (with DAC two consecutive pivot columns may share j & 1)
+    bool done = !mine;
+    int pos = cm;
+    if (done && t < N) STEP[t] = -1;              // T, p and removed species: diagonal rows, solved in closed form
+    if (t == 0) WS(XS)[1] = 1.0 / dg;
+    int par = 1;      // exchange buffer, toggled per pivot column
 #pragma unroll 1
-    for (ColsUp cu(DAC, act, nSp); cu.next<DAC>();) {
-        const int j = cu.j;
+    for (int j = 0; j < Ns; ++j) {
         par ^= 1;
         const double piv = done ? 0.0 : row[j];
         const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
         const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
         // one reduction on the top 32 bits of the key decides the warp's candidate whenever that maximum is unique
         // (the common case); ties in the top half fall through to the exact 64-bit + position comparison
-        const unsigned mh = __reduce_max_sync(0xffffffffu, hi);
+        const unsigned mh = __reduce_max_sync(g.mask, hi);
         const bool c1 = hi == mh;
         bool win = c1;
-        if (__popc(__ballot_sync(0xffffffffu, c1)) != 1) {
-            const unsigned ml = __reduce_max_sync(0xffffffffu, c1 ? lo : 0u);
+        if (__popc(__ballot_sync(g.mask, c1)) != 1) {
+            const unsigned ml = __reduce_max_sync(g.mask, c1 ? lo : 0u);
             const bool c2 = c1 && lo == ml;
             const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
-            const unsigned mp = __reduce_max_sync(0xffffffffu, pp);
+            const unsigned mp = __reduce_max_sync(g.mask, pp);
             win = c2 && pp == mp;
         }
         if (win) {
             double* slot = XCH + (g.warp * 2 + par) * 4;
             slot[0] = __longlong_as_double((long long)key);
             reinterpret_cast<int*>(slot + 1)[0] = pos;
-            reinterpret_cast<int*>(slot + 1)[1] = t;
+            reinterpret_cast<int*>(slot + 1)[1] = cm;
             slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
         }
         g.sync();
@@ -515,41 +566,41 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
         const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
         const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
         const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
-        const double* sw = (k1 > k0 || (k1 == k0 && p1 > p0)) ? s1 : s0;
+        const double* sw = (Grp::kTwoWarps && (k1 > k0 || (k1 == k0 && p1 > p0))) ? s1 : s0;   // one warp: its candidate is the pivot
         const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
-        const int ptid = reinterpret_cast<const int*>(sw + 1)[1];
+        const int prw = reinterpret_cast<const int*>(sw + 1)[1];
         const double rd = sw[2];
-        if (t == ptid) {
+        if (!done && cm == prw) {
             done = true; STEP[t] = j; RD[j] = rd;
             if (piv == 0.0) row[j] = LB_SMALL;
         } else if (!done) {
             if (pos == j) pos = ppos;
             const double l = piv * rd;
             row[j] = l;
-            const double* __restrict__ prow = A + ptid * lda;
-            double* __restrict__ mine = row;
+            const double* __restrict__ prow = A + prw * ldc;
+            double* __restrict__ mine_ = row;
             int k = j + 1;
             // batches of eight, then four: all loads first, so the stores of one batch never wait behind its loads
 #pragma unroll 1
-            for (; k + 7 <= nSp; k += 8) {
+            for (; k + 7 <= Ns; k += 8) {
                 const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
                 const double p4 = prow[k + 4], p5 = prow[k + 5], p6 = prow[k + 6], p7 = prow[k + 7];
-                const double r0 = mine[k], r1 = mine[k + 1], r2 = mine[k + 2], r3 = mine[k + 3];
-                const double r4 = mine[k + 4], r5 = mine[k + 5], r6 = mine[k + 6], r7 = mine[k + 7];
-                mine[k] = fma(-l, p0, r0); mine[k + 1] = fma(-l, p1, r1);
-                mine[k + 2] = fma(-l, p2, r2); mine[k + 3] = fma(-l, p3, r3);
-                mine[k + 4] = fma(-l, p4, r4); mine[k + 5] = fma(-l, p5, r5);
-                mine[k + 6] = fma(-l, p6, r6); mine[k + 7] = fma(-l, p7, r7);
+                const double r0 = mine_[k], r1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                const double r4 = mine_[k + 4], r5 = mine_[k + 5], r6 = mine_[k + 6], r7 = mine_[k + 7];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, r1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
+                mine_[k + 4] = fma(-l, p4, r4); mine_[k + 5] = fma(-l, p5, r5);
+                mine_[k + 6] = fma(-l, p6, r6); mine_[k + 7] = fma(-l, p7, r7);
             }
 #pragma unroll 1
-            for (; k + 3 <= nSp; k += 4) {
+            for (; k + 3 <= Ns; k += 4) {
                 const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
-                const double r0 = mine[k], r1 = mine[k + 1], r2 = mine[k + 2], r3 = mine[k + 3];
-                mine[k] = fma(-l, p0, r0); mine[k + 1] = fma(-l, p1, r1);
-                mine[k + 2] = fma(-l, p2, r2); mine[k + 3] = fma(-l, p3, r3);
+                const double r0 = mine_[k], r1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, r1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
             }
 #pragma unroll 1
-            for (; k <= nSp; ++k) mine[k] = fma(-l, prow[k], mine[k]);
+            for (; k <= Ns; ++k) mine_[k] = fma(-l, prow[k], mine_[k]);
         }
     }
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
@@ -559,35 +610,36 @@ __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
 
 // x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out)
 template <bool DAC>
-__device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
+static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     const Grp g(base);
-    const int nSp = cx->S.nSp, t = g.tid, lda = cx->lda, N = cx->nEqn;
-    const double* row = WS(A) + t * lda;
+    const int nSp = cx->S.nSp, t = g.tid, N = cx->nEqn;
+    const Compact<DAC> cp(cx, base);
+    const int Ns = cp.Ns;
+    const bool sp = t < nSp && cp.kept(t);
+    const double* row = WS(A) + (sp ? cp.index(t) : 0) * cp.ldc;
     const double* RD = WS(RD);
     double* BS = WS(BS);
+    const int* SPOF = reinterpret_cast<const int*>(WS(STEP)) + N + (N & 1);
     g.sync();
     const int step = t < N ? reinterpret_cast<const int*>(WS(STEP))[t] : -1;
+    const double rdg = WS(XS)[1];                   // 1 / dg: the diagonal rows (T, p, removed species)
     double bt = t < N ? x[t] : 0.0;
-    const unsigned long long act = DAC ? reinterpret_cast<const unsigned long long*>(WS(MSK))[(cx->S.nR + 63) >> 6] : ~0ull;
-    const bool sp = t < nSp && ((act >> t) & 1ull);
-    if (t < nSp && !sp) x[t] = bt * RD[t];          // removed species: decoupled diagonal row
+    if (t < nSp && !sp) x[t] = bt * rdg;            // removed species: decoupled diagonal row
     // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
-    for (ColsUp cu(DAC, act, nSp); cu.next<DAC>();) {
-        const int j = cu.j;
+    for (int j = 0; j < Ns; ++j) {
         if (step == j) BS[j] = bt;
         g.sync();
         if (sp && step > j) bt = fma(-row[j], BS[j], bt);
     }
     // backward substitution: p and T first (diagonal rows), then the species columns in descending order
-    if (t == nSp + 1) x[t] = bt * RD[t];
-    if (t == nSp) { const double v = bt * RD[t]; BS[t] = v; x[t] = v; }
+    if (t == nSp + 1) x[t] = bt * rdg;
+    if (t == nSp) { const double v = bt * rdg; BS[Ns] = v; x[t] = v; }
     g.sync();
-    if (sp) bt = fma(-row[nSp], BS[nSp], bt);
+    if (sp) bt = fma(-row[Ns], BS[Ns], bt);
 #pragma unroll 1
-    for (ColsDown cd(act, nSp); cd.next<DAC>();) {
-        const int j = cd.j;
-        if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[j] = v; }
+    for (int j = Ns - 1; j >= 0; --j) {
+        if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[DAC ? SPOF[j] : j] = v; }
         g.sync();
         if (sp && step < j) bt = fma(-row[j], BS[j], bt);
     }
@@ -603,7 +655,7 @@ __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
 // queued once, in the reference's order: neighbours in first-appearance order) with R_B = max(R_B, R_u r_uB).
 // Uses the matrix region for the numerators and V1..V4 as scratch: call before the integration starts.
 // ------------------------------------------------------------------------------------------------
-__device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double* y) {
+static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double* y) {
     const Grp g(base);
     const SMech& S = cx->S;
     const int nSp = S.nSp, nR = S.nR, t = g.tid;
@@ -743,18 +795,14 @@ __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const double
 // ------------------------------------------------------------------------------------------------
 // integrators (control flow identical to lbchem_kernels_v2.cu; only the heavy routines are calls)
 // ------------------------------------------------------------------------------------------------
-struct Cell { int fail; double theta; int kTarg; int f0valid; };
-struct StepState { int forward, first, last, reject, prevReject; double dxTry, dxDid; };
 
-__constant__ int c_nSeq[12] = {2, 3, 4, 6, 8, 12, 16, 24, 32, 48, 64, 96};
-__constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434, 625};
 
 #define CNT(i) (reinterpret_cast<int*>(WS(CNT))[i])
 
 // one Rosenbrock34 attempt (A.4) from Y0=V0 with step dx; result in V1. The sparse Jacobian (and dfdx in V3)
 // of the step start are re-used after a rejected attempt: the reference recomputes identical values.
 template <bool DAC>
-__device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dx) {
+static __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dx) {
     const double a21 = 2, a31 = 48.0 / 25.0, a32 = 6.0 / 25.0, c21 = -8, c31 = 372.0 / 25.0, c32 = 12.0 / 5.0,
                  c41 = -112.0 / 125.0, c42 = -54.0 / 125.0, c43 = -2.0 / 5.0, b1 = 19.0 / 9.0, b2 = 1.0 / 2.0,
                  b3 = 25.0 / 108.0, b4 = 125.0 / 108.0, e1 = 34.0 / 108.0, e2 = 7.0 / 36.0, e3 = 0, e4 = 125.0 / 108.0,
@@ -793,7 +841,7 @@ __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const Ctx* cx,
 
 // adaptiveSolver::solve (A.3)
 template <bool DAC>
-__device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, double& dxTry) {
+static __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, double& dxTry) {
     const double safeScale = 0.9, alphaInc = 0.2, alphaDec = 0.25, minScale = 0.2, maxScale = 10;
     const int t = g.tid, N = cx->nEqn;
     double dx = dxTry, err = 0.0;
@@ -825,7 +873,7 @@ __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* cx, doub
 // `phase` keeps derivatives() and lu_solve() at one call site each: phase 1 = the stability check of the
 // second sub-step (solves dyc), phase 0 = the regular Euler increment (solves dy).
 template <bool DAC>
-__device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k) {
+static __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k) {
     const int t = g.tid, N = cx->nEqn;
     const int nSteps = c_nSeq[k];
     const double dx = dxTot / nSteps;
@@ -886,14 +934,14 @@ __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, 
     return ok;
 }
 
-__device__ __forceinline__ double seulex_coeff(int k, int l) {
+static __device__ __forceinline__ double seulex_coeff(int k, int l) {
     const double ratio = (double)c_nSeq[k] / c_nSeq[l];
     return 1 / (ratio - 1);
 }
 
 // seulex::solve (A.5); y = V0
 template <bool DAC>
-__device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, StepState& step, int& attempts) {
+static __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double& x, StepState& step, int& attempts) {
     const int t = g.tid, N = cx->nEqn;
     const DevOpts& O = cx->O;
     const int kMaxx = 11;
@@ -1040,7 +1088,7 @@ __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx, double
 
 // ODESolver::solve (A.2); y = V0
 template <int SOLVER, bool DAC>
-__device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double xStart, double xEnd, double& dxTry) {
+static __device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* base, Cell& cs, double xStart, double xEnd, double& dxTry) {
     StepState step = {1, 1, 0, 0, 0, dxTry, 0.0};
     double x = xStart;
     int attempts = 0;
@@ -1073,12 +1121,9 @@ __device__ __forceinline__ void ode_solve(const Grp& g, const Ctx* cx, double* b
 }
 
 
-// smem layout: [Ctx (padded to 512 B)] [mechanism blob] [groups x workspace]
-constexpr int CTX_BYTES = 512;
-static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
 
 template <int SOLVER, bool DAC>
-__global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
+static __device__ __forceinline__ void integrate_body(const V2Mech& M, const DevOpts& O, const BatchArgs& B, int wsDoubles) {
     extern __shared__ double smem[];
     unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
     {
@@ -1191,7 +1236,7 @@ __global__ void __launch_bounds__(TPC * 6, 1) integrate_v3_kernel(V2Mech M, DevO
 //   tc = nReaction * sum_i c_i / (SMALL + sum_r (sum_rhs nu) * kf_r * prod_lhs c^e)
 // Same staging, workspace layout and rate sweep as the integration kernel; one cell per 64-thread group.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, double* tcOut) {
+static __device__ __forceinline__ void tc_body(const V2Mech& M, const DevOpts& O, const BatchArgs& B, int wsDoubles, double* tcOut) {
     extern __shared__ double smem[];
     unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
     {
@@ -1248,8 +1293,8 @@ __global__ void __launch_bounds__(TPC * 6, 1) tc_v3_kernel(V2Mech M, DevOpts O, 
 // can be localised. One state per 64-thread group. Layouts as in include/lbchem.h (kf / kr come out in packed reaction
 // order; the host maps them back).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TPC * 6, 1) probe_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, int kind, int nItems,
-                                                              const double* in, int inStride, double* out, int outStride) {
+static __device__ __forceinline__ void probe_body(const V2Mech& M, const DevOpts& O, const BatchArgs& B, int wsDoubles, int kind, int nItems,
+                                                   const double* in, int inStride, double* out, int outStride) {
     extern __shared__ double smem[];
     unsigned char* sm = reinterpret_cast<unsigned char*>(smem);
     {
@@ -1317,6 +1362,22 @@ __global__ void __launch_bounds__(TPC * 6, 1) probe_v3_kernel(V2Mech M, DevOpts 
     }
 }
 
+};   // struct K<TPC>
+
+template <int TPC, int SOLVER, bool DAC>
+__global__ void __launch_bounds__(384, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
+    K<TPC>::template integrate_body<SOLVER, DAC>(M, O, B, wsDoubles);
+}
+template <int TPC>
+__global__ void __launch_bounds__(384, 1) tc_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, double* tcOut) {
+    K<TPC>::tc_body(M, O, B, wsDoubles, tcOut);
+}
+template <int TPC>
+__global__ void __launch_bounds__(384, 1) probe_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, int kind, int nItems,
+                                                          const double* in, int inStride, double* out, int outStride) {
+    K<TPC>::probe_body(M, O, B, wsDoubles, kind, nItems, in, inStride, out, outStride);
+}
+
 }  // namespace v3
 
 // ------------------------------------------------------------------------------------------------
@@ -1330,51 +1391,95 @@ int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol) {
     return v3::ctx_layout(c, M);
 }
 
-bool lb_v3_supported(const V2Mech& M) { return M.nEqn <= v3::TPC && M.nEqn >= 3; }
+bool lb_v3_supported(const V2Mech& M) { return M.nEqn <= 64 && M.nEqn >= 3 && M.tpc >= M.nEqn; }
 int lb_v3_ctx_bytes() { return v3::CTX_BYTES; }
+int lb_v3_max_groups(int tpc) { return 384 / tpc; }
 
-template <int SOLVER, bool DAC>
-static cudaError_t v3_attr(size_t smemBytes) {
-    return cudaFuncSetAttribute(v3::integrate_v3_kernel<SOLVER, DAC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+namespace {
+template <int TPC, int SOLVER, bool DAC>
+cudaError_t attr1(size_t smemBytes) {
+    return cudaFuncSetAttribute(v3::integrate_v3_kernel<TPC, SOLVER, DAC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
 }
-
-// both variants of the solver's kernel: full mechanism, and DAC-reduced (selected per launch by M.dac)
-cudaError_t lb_v3_configure(int solver, size_t smemBytes) {
-    cudaError_t e = solver == LBCHEM_SOLVER_SEULEX ? v3_attr<LBCHEM_SOLVER_SEULEX, false>(smemBytes)
-                                                   : v3_attr<LBCHEM_SOLVER_ROSENBROCK34, false>(smemBytes);
-    if (e != cudaSuccess) return e;
-    return solver == LBCHEM_SOLVER_SEULEX ? v3_attr<LBCHEM_SOLVER_SEULEX, true>(smemBytes)
-                                          : v3_attr<LBCHEM_SOLVER_ROSENBROCK34, true>(smemBytes);
+template <int TPC>
+cudaError_t attr_tpc(int solver, size_t smemBytes) {
+    cudaError_t e = solver == LBCHEM_SOLVER_SEULEX ? attr1<TPC, LBCHEM_SOLVER_SEULEX, false>(smemBytes)
+                                                   : attr1<TPC, LBCHEM_SOLVER_ROSENBROCK34, false>(smemBytes);
+    if (e != cudaSuccess || TPC != 64) return e;
+    // the DAC-reduced variant exists for 64-thread groups only (selected per launch by M.dac)
+    return solver == LBCHEM_SOLVER_SEULEX ? attr1<64, LBCHEM_SOLVER_SEULEX, true>(smemBytes)
+                                          : attr1<64, LBCHEM_SOLVER_ROSENBROCK34, true>(smemBytes);
 }
+template <int TPC>
+cudaError_t launch_tpc(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
+                       const BatchArgs& B, cudaStream_t s) {
+    const int block = groups * TPC;
+    if (solver == LBCHEM_SOLVER_SEULEX) v3::integrate_v3_kernel<TPC, LBCHEM_SOLVER_SEULEX, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+    else v3::integrate_v3_kernel<TPC, LBCHEM_SOLVER_ROSENBROCK34, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+    return cudaGetLastError();
+}
+}  // namespace
 
-cudaError_t lb_v3_launch(int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
-                         const BatchArgs& B, cudaStream_t s) {
-    const int block = groups * v3::TPC;
-    if (solver == LBCHEM_SOLVER_SEULEX) {
-        if (M.dac) v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX, true><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
-        else v3::integrate_v3_kernel<LBCHEM_SOLVER_SEULEX, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
-    } else {
-        if (M.dac) v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, true><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
-        else v3::integrate_v3_kernel<LBCHEM_SOLVER_ROSENBROCK34, false><<<grid, block, smemBytes, s>>>(M, O, B, wsDoubles);
+cudaError_t lb_v3_configure(int tpc, int solver, size_t smemBytes) {
+    switch (tpc) {
+        case 8: return attr_tpc<8>(solver, smemBytes);
+        case 16: return attr_tpc<16>(solver, smemBytes);
+        case 32: return attr_tpc<32>(solver, smemBytes);
+        default: return attr_tpc<64>(solver, smemBytes);
     }
-    return cudaGetLastError();
 }
 
-cudaError_t lb_v3_tc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+cudaError_t lb_v3_launch(int tpc, int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
+                         const BatchArgs& B, cudaStream_t s) {
+    if (M.dac) {
+        if (tpc != 64) return cudaErrorInvalidValue;
+        if (solver == LBCHEM_SOLVER_SEULEX) v3::integrate_v3_kernel<64, LBCHEM_SOLVER_SEULEX, true><<<grid, groups * 64, smemBytes, s>>>(M, O, B, wsDoubles);
+        else v3::integrate_v3_kernel<64, LBCHEM_SOLVER_ROSENBROCK34, true><<<grid, groups * 64, smemBytes, s>>>(M, O, B, wsDoubles);
+        return cudaGetLastError();
+    }
+    switch (tpc) {
+        case 8: return launch_tpc<8>(solver, grid, groups, smemBytes, wsDoubles, M, O, B, s);
+        case 16: return launch_tpc<16>(solver, grid, groups, smemBytes, wsDoubles, M, O, B, s);
+        case 32: return launch_tpc<32>(solver, grid, groups, smemBytes, wsDoubles, M, O, B, s);
+        default: return launch_tpc<64>(solver, grid, groups, smemBytes, wsDoubles, M, O, B, s);
+    }
+}
+
+namespace {
+template <int TPC>
+cudaError_t tc_tpc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B, double* tcOut, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(v3::tc_v3_kernel<TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (e != cudaSuccess) return e;
+    v3::tc_v3_kernel<TPC><<<grid, groups * TPC, smemBytes, s>>>(M, O, B, wsDoubles, tcOut);
+    return cudaGetLastError();
+}
+template <int TPC>
+cudaError_t probe_tpc(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+                      int kind, int nItems, const double* in, int inStride, double* out, int outStride, cudaStream_t s) {
+    cudaError_t e = cudaFuncSetAttribute(v3::probe_v3_kernel<TPC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
+    if (e != cudaSuccess) return e;
+    v3::probe_v3_kernel<TPC><<<grid, groups * TPC, smemBytes, s>>>(M, O, B, wsDoubles, kind, nItems, in, inStride, out, outStride);
+    return cudaGetLastError();
+}
+}  // namespace
+
+cudaError_t lb_v3_tc(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
                      double* tcOut, cudaStream_t s) {
-    cudaError_t e = cudaFuncSetAttribute(v3::tc_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-    if (e != cudaSuccess) return e;
     V2Mech Mm = M; Mm.dac = nullptr;
-    v3::tc_v3_kernel<<<grid, groups * v3::TPC, smemBytes, s>>>(Mm, O, B, wsDoubles, tcOut);
-    return cudaGetLastError();
+    switch (tpc) {
+        case 8: return tc_tpc<8>(grid, groups, smemBytes, wsDoubles, Mm, O, B, tcOut, s);
+        case 16: return tc_tpc<16>(grid, groups, smemBytes, wsDoubles, Mm, O, B, tcOut, s);
+        case 32: return tc_tpc<32>(grid, groups, smemBytes, wsDoubles, Mm, O, B, tcOut, s);
+        default: return tc_tpc<64>(grid, groups, smemBytes, wsDoubles, Mm, O, B, tcOut, s);
+    }
 }
 
-
-cudaError_t lb_v3_probe(int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
+cudaError_t lb_v3_probe(int tpc, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O, const BatchArgs& B,
                         int kind, int nItems, const double* in, int inStride, double* out, int outStride, cudaStream_t s) {
-    cudaError_t e = cudaFuncSetAttribute(v3::probe_v3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smemBytes);
-    if (e != cudaSuccess) return e;
     V2Mech Mm = M; Mm.dac = nullptr;
-    v3::probe_v3_kernel<<<grid, groups * v3::TPC, smemBytes, s>>>(Mm, O, B, wsDoubles, kind, nItems, in, inStride, out, outStride);
-    return cudaGetLastError();
+    switch (tpc) {
+        case 8: return probe_tpc<8>(grid, groups, smemBytes, wsDoubles, Mm, O, B, kind, nItems, in, inStride, out, outStride, s);
+        case 16: return probe_tpc<16>(grid, groups, smemBytes, wsDoubles, Mm, O, B, kind, nItems, in, inStride, out, outStride, s);
+        case 32: return probe_tpc<32>(grid, groups, smemBytes, wsDoubles, Mm, O, B, kind, nItems, in, inStride, out, outStride, s);
+        default: return probe_tpc<64>(grid, groups, smemBytes, wsDoubles, Mm, O, B, kind, nItems, in, inStride, out, outStride, s);
+    }
 }

@@ -46,6 +46,7 @@ struct V2Mech {
     const int* jthrN;                    // [64] number of terms of thread t
     int jMaxTerms;
     const int* dac;                      // DAC program (lb_dac_program) when reduction is active, else null (v3 kernel)
+    int tpc;                             // threads per cell of the compact-code kernel: 8, 16, 32 or 64 (>= nEqn)
     int tbRows;                          // rows of the seulex extrapolation table held per cell
     int wsDoubles;                       // per-cell workspace in doubles
 };

@@ -2,6 +2,7 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <map>
 #include <string>
@@ -352,7 +353,10 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         P.jterm = jterm; P.thrEnt = thrEnt; P.thrN = thrN; P.maxT = maxT;
         return P;
     };
-    Prog P64 = deal(V2_TPC);
+    // group width: the smallest of 8 / 16 / 32 / 64 threads that gives every equation its own thread
+    M.tpc = N <= 8 ? 8 : (N <= 16 ? 16 : (N <= 32 ? 32 : 64));
+    if (const char* e = getenv("LBCHEM_V3_TPC")) { const int q = atoi(e); if ((q == 8 || q == 16 || q == 32 || q == 64) && q >= N) M.tpc = q; }
+    Prog P64 = deal(M.tpc);
     M.jMaxTerms = P64.maxT;
     M.blobBytes = (int)B.b.size();
     auto up = [&](const void* src, size_t bytes, const void** dst) -> bool {
@@ -364,7 +368,7 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         return true;
     };
     const void *dBlob, *dTerm, *dEnt, *dN, *dD;
-    for (int q = 0; q < 8 * V2_TPC; ++q) dterm.push_back(0ull);          // read-ahead padding
+    for (int q = 0; q < 8 * 64; ++q) dterm.push_back(0ull);          // read-ahead padding
     if (!up(B.b.data(), B.b.size(), &dBlob) || !up(P64.jterm.data(), P64.jterm.size() * 4, &dTerm) || !up(dterm.data(), dterm.size() * 8, &dD) ||
         !up(P64.thrEnt.data(), P64.thrEnt.size() * 4, &dEnt) || !up(P64.thrN.data(), P64.thrN.size() * 4, &dN)) {
         err = "cudaMalloc/cudaMemcpy failed while uploading the packed mechanism";
