@@ -187,6 +187,19 @@ int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy,
                        double* deltaTChem, double* RR, double* Tout, double* cost,
                        int32_t* status, void* stream);
 
+/*
+ * The same integration for a MISS LIST: only the cells index[0 .. n_index) of the field-major arrays are integrated (gather
+ * on load, scatter on store: RR / deltaTChem / Tout / cost / status are written at those cells only, every other entry
+ * is left as it is). This is the device half of LoadBalancedTDAC with `tabulation{active on;}`: the host ISAT filter
+ * (LoadBalancedTDACChemistryModel.C:683-740) retrieves what it can and lists the misses; no repacking of the fields.
+ * DEVICE pointers (index too), stream-ordered; arrays must cover max(index) + 1 cells, ldy as in lbchem_solve_batch.
+ */
+int lbchem_solve_batch_indexed(lbchem_handle h, int64_t n_index, const int32_t* index, int64_t ldy,
+                               const double* Y, const double* T, const double* p, const double* rho,
+                               const double* deltaT, double deltaT_uniform,
+                               double* deltaTChem, double* RR, double* Tout, double* cost,
+                               int32_t* status, void* stream);
+
 /* Same call with HOST pointers: the cells are cut into chunks that cycle through three streams (H2D, integrate, D2H),
  * copied straight from / to the caller's arrays. With pinned (page-locked) caller arrays the copies of one chunk overlap
  * the integration of its neighbours; with pageable arrays every copy blocks the host and the chunks run one after the

@@ -163,6 +163,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
            C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.lbchem_solve_batch.argtypes = sig + [C.c_void_p]
     lib.lbchem_solve_batch_host.argtypes = sig
+    lib.lbchem_solve_batch_indexed.argtypes = [H, C.c_int64, C.c_void_p, C.c_int64] + [C.c_void_p] * 5 + [C.c_double] + [C.c_void_p] * 6
     lib.lbchem_get_stats.argtypes = [H, C.POINTER(Stats)]
     lib.lbchem_set_reduction.argtypes = [H, C.c_int32, C.c_double, C.c_int32, _ip]
     lib.lbchem_get_active_species.argtypes = [H, C.c_int64, _ip]
@@ -224,7 +225,7 @@ def lb_options(update_iter=0, min_fraction=0.02, tdac=False, balance=True) -> Lb
 
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
-    "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_get_stats lbchem_balance_plan "
+    "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_solve_batch_indexed lbchem_get_stats lbchem_balance_plan "
     "lbchem_cells_to_send lbchem_cells_to_send_device lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc "
     "lbchem_lb_default_options lbchem_lb_nccl_unique_id lbchem_lb_create_nccl lbchem_lb_create_transport lbchem_lb_create_loopback "
     "lbchem_lb_set_options lbchem_lb_destroy lbchem_lb_last_error lbchem_lb_solve lbchem_lb_solve_host lbchem_lb_get_info lbchem_lb_get_plan"
@@ -356,6 +357,18 @@ class Chemistry:
                                          ptr(deltaTChem), ptr(RR), ptr(Tout), ptr(cost), ptr(status),
                                          C.c_void_p(int(stream)))
         self._check(rc, "lbchem_solve_batch")
+
+    def solve_indexed(self, index, ldy, Y, T, p, rho, deltaT, deltaTChem, RR, Tout=None, cost=None, status=None, stream=0):
+        """Integrate only the cells listed in ``index`` (int32 CUDA tensor): the ISAT miss list (lbchem_solve_batch_indexed)."""
+        ptr = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        if isinstance(deltaT, (int, float)):
+            dT_arr, dT_u = None, float(deltaT)
+        else:
+            dT_arr, dT_u = deltaT, 0.0
+        rc = self.lib.lbchem_solve_batch_indexed(self.h, int(index.shape[0]), ptr(index), int(ldy), ptr(Y), ptr(T), ptr(p), ptr(rho),
+                                                 ptr(dT_arr), dT_u, ptr(deltaTChem), ptr(RR), ptr(Tout), ptr(cost), ptr(status),
+                                                 C.c_void_p(int(stream)))
+        self._check(rc, "lbchem_solve_batch_indexed")
 
     def qdot_device(self, n, ldy, RR, Qdot, stream=0):
         """Qdot [W/m3] from the RR block of the last solve (torch CUDA tensors or anything with data_ptr())."""

@@ -553,6 +553,28 @@ int lbchem_solve_batch(lbchem_handle h, int64_t n, int64_t ldy, const double* Y,
     return LBCHEM_OK;
 }
 
+int lbchem_solve_batch_indexed(lbchem_handle h, int64_t n_index, const int32_t* index, int64_t ldy, const double* Y, const double* T,
+                               const double* p, const double* rho, const double* deltaT, double deltaT_uniform, double* deltaTChem,
+                               double* RR, double* Tout, double* cost, int32_t* status, void* stream) {
+    if (!h) return LBCHEM_E_INVALID;
+    if (n_index < 0 || (n_index > 0 && (!index || !Y || !T || !p || !rho || !deltaTChem || !RR)) || (!deltaT && !(deltaT_uniform > 0)))
+        return fail(h, LBCHEM_E_INVALID, "bad batch arguments");
+    CK(cudaSetDevice(h->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    h->launches = 0; h->hostPath = false; h->lastN = 0;
+    CK(cudaMemsetAsync(h->dStats, 0, 8 * sizeof(unsigned long long), s));
+    CK(cudaEventRecord(h->ev0, s));
+    if (n_index > 0) {
+        CellSeg a = make_seg(n_index, ldy, Y, T, p, rho, deltaT, deltaTChem, RR, Tout, cost, status, nullptr);
+        a.index = index;
+        int rc = lb_launch_batch(h, &a, nullptr, deltaT_uniform, nullptr, h->dQueue, h->dScratch, s);
+        if (rc != LBCHEM_OK) return rc;
+    }
+    CK(cudaEventRecord(h->ev1, s));
+    h->evValid = true;
+    return LBCHEM_OK;
+}
+
 static int slot_reserve(lbchem_handle h, Slot& s, long long cap, int nSp) {
     if (!s.stream) {
         CK(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));

@@ -66,6 +66,7 @@ struct CellSeg {
     const double* Y; const double* T; const double* p; const double* rho; const double* deltaT;
     double* deltaTChem; double* RR; double* Tout; double* cost; int* status;
     int* nActive;                // optional: number of active species DAC kept for each cell (NsDAC_)
+    const int* index;            // optional miss list: queue position q of this segment integrates cell index[q]
 };
 
 // per-batch arguments. A batch is one or two segments handed out through ONE work queue: the load-balanced step

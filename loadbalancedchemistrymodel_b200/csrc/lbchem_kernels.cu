@@ -992,7 +992,8 @@ __global__ void __launch_bounds__(TPC * (TPC < 32 ? 16 : 8)) integrate_kernel(De
             q = reinterpret_cast<unsigned long long*>(g.red)[7];
         }
         if (q >= (unsigned long long)B.a.n) break;
-        const long long cell = B.order ? (long long)B.order[q] : (long long)q;
+        long long cell = B.order ? (long long)B.order[q] : (long long)q;
+        if (B.a.index) cell = B.a.index[cell];
         const double T0 = B.a.T[cell];
         const double p0 = B.a.p[cell];
         const double rho = B.a.rho[cell];

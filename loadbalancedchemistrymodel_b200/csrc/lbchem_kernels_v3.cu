@@ -1161,6 +1161,7 @@ static __device__ __forceinline__ void integrate_body(const V2Mech& M, const Dev
         const bool second = cell >= B.a.n;
         if (second) cell -= B.a.n;
 #define SEG(f) (second ? B.b.f : B.a.f)
+        { const int* ix = SEG(index); if (ix) cell = ix[cell]; }     // ISAT miss list: only the listed cells are integrated
         const double* __restrict__ Yp = SEG(Y);
         double* __restrict__ RRp = SEG(RR);
         const long long ldy = SEG(ldy);

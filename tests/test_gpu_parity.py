@@ -603,3 +603,35 @@ def test_two_ranks_on_one_gpu_redistribute_real_cells(gri, flame, tdac):
         m.close()
     for c in chems + [single]:
         c.close()
+
+
+def test_miss_list_integrates_only_the_listed_cells(gri, flame):
+    """lbchem_solve_batch_indexed: the device half of ISAT-aware batching (reference
+    LoadBalancedTDACChemistryModel.C:683-740 builds the miss list on the host). A random 30 % of the fixture cells are
+    'misses': they come back exactly as in the full solve, every other cell's outputs stay untouched."""
+    import torch
+    dev = torch.device("cuda:0")
+    sel = np.arange(flame["T"].shape[0])
+    Y, T, p, rho = _state(gri, flame, sel)
+    n = sel.size
+    chem = capi.Chemistry(gri, capi.default_options(solver="seulex", abs_tol=1e-12, rel_tol=1e-1))
+    full = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+    rng = np.random.default_rng(21)
+    miss = np.sort(rng.choice(n, int(0.3 * n), replace=False)).astype(np.int32)
+    rng.shuffle(miss)                                                   # any order
+    tY, tT, tp, trho = (torch.from_numpy(np.ascontiguousarray(a)).to(dev) for a in (Y, T, p, rho))
+    dtc = torch.full((n,), DTCHEM, dtype=torch.float64, device=dev)
+    RR = torch.full((gri.n_species, n), -7.0, dtype=torch.float64, device=dev)
+    To = torch.full((n,), -7.0, dtype=torch.float64, device=dev); co = torch.full((n,), -7.0, dtype=torch.float64, device=dev)
+    so = torch.full((n,), -7, dtype=torch.int32, device=dev)
+    chem.solve_indexed(torch.from_numpy(miss).to(dev), n, tY, tT, tp, trho, DT, dtc, RR, To, co, so)
+    torch.cuda.synchronize()
+    st = chem.stats()
+    assert st["n_cells"] == miss.size
+    hit = np.ones(n, bool); hit[miss] = False
+    RRh, dtch, Toh, coh, soh = RR.cpu().numpy(), dtc.cpu().numpy(), To.cpu().numpy(), co.cpu().numpy(), so.cpu().numpy()
+    assert np.array_equal(RRh[:, miss], full["RR"][:, miss]) and np.array_equal(dtch[miss], full["deltaTChem"][miss])
+    assert np.array_equal(Toh[miss], full["T"][miss]) and np.array_equal(coh[miss], full["cost"][miss]) and (soh[miss] == 0).all()
+    assert (RRh[:, hit] == -7.0).all() and (dtch[hit] == DTCHEM).all() and (Toh[hit] == -7.0).all() and (soh[hit] == -7).all()
+    chem.solve_indexed(torch.zeros(0, dtype=torch.int32, device=dev), n, tY, tT, tp, trho, DT, dtc, RR, To, co, so)   # empty list
+    chem.close()
