@@ -382,7 +382,7 @@ const char* lbchem_last_error(lbchem_handle h) { return h ? h->err.c_str() : "nu
 int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int32_t n_init, const int32_t* init_species) {
     if (!h) return LBCHEM_E_INVALID;
     CK(cudaSetDevice(h->device));
-    if (!active) { h->dacOn = false; h->V2.dac = nullptr; return LBCHEM_OK; }
+    if (!active) { h->dacOn = false; h->V2.dac = nullptr; return configure(h); }     // the workspace layout depends on it
     if (h->dacProg.empty() || !h->v2Built || h->V2.tpc != 64)
         return fail(h, LBCHEM_E_UNSUPPORTED, "DAC reduction needs the packed mechanism of the compact-code kernel (nSp <= 62, integer stoichiometry)");
     if (!(tolerance > 0.0) || n_init < 1 || n_init > 8 || !init_species)
@@ -403,7 +403,7 @@ int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int3
     CK(cudaMemcpy(h->dDac, h->dacProg.data(), h->dacProg.size() * sizeof(int), cudaMemcpyHostToDevice));
     h->V2.dac = h->dDac;
     h->dacOn = true;
-    return LBCHEM_OK;
+    return configure(h);        // the reduced kernel's workspace holds the reaction masks and the enabled-reaction list
 }
 
 int lbchem_qdot(lbchem_handle h, int64_t n, int64_t ldy, const double* RR, double* Qdot, void* stream) {

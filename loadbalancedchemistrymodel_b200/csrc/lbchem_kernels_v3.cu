@@ -61,7 +61,7 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA, oMSK, oSX;
+    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA, oMSK, oSX, oRL;
     const unsigned* jterm; const unsigned long long* dterm; int nD; const int* jthrEnt; const int* jthrN;
     const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
@@ -72,7 +72,11 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
     int p = 32;                               // reduction scratch
     c.oXCH = p; p += 16; c.oXS = p; p += 2; c.oCNT = p; p += 4;
-    c.oMSK = p; p += (M.nR + 63) / 64 + 1;    // DAC: disabled-reaction bits (by packed position), then the active-species word
+    c.oMSK = p; c.oRL = p;
+    if (M.dac) {                              // DAC only (the reduced instantiation of the kernel):
+        p += (M.nR + 63) / 64 + 1;            //   disabled-reaction bits (by packed position), then the active-species word
+        c.oRL = p; p += 1 + (M.nR + 3) / 4;   //   int count + 16-bit list of the packed positions of the ENABLED reactions
+    }
     c.oV = p; p += 9 * N;
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
     c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
@@ -238,11 +242,17 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
     const unsigned long long* MSK = reinterpret_cast<const unsigned long long*>(WS(MSK));
     constexpr bool dac = DAC;
 #define RX_OFF(p) (dac && ((MSK[(p) >> 6] >> ((p) & 63)) & 1ull))
+    // DAC: the sweep walks the compacted list of enabled reactions (half of GRI is typically switched off: three rounds
+    // of 64 instead of six); OM of a disabled reaction was zeroed once by dac_reduce and is never touched again
+    const int nLoop = dac ? reinterpret_cast<const int*>(WS(RL))[0] : nR;
+    const unsigned short* RL = reinterpret_cast<const unsigned short*>(WS(RL) + 1);
+#define RX_AT(q) (dac ? (int)RL[q] : (q))
     // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
 #pragma unroll 1
-    for (int p = g.tid; p < nR; p += TPC) {
+    for (int q = g.tid; q < nLoop; q += TPC) {
+        const int p = RX_AT(q);
         double val = 1.0;
-        if (V2_HASEXP(S.info[p]) && !RX_OFF(p)) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
+        if (V2_HASEXP(S.info[p])) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
         OM[p] = val;
     }
     g.sync();
@@ -277,8 +287,8 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
     const double kcFloor = cx->O.kcFloor;
     double* KF = WS(A); double* KR = KF + nR;
 #pragma unroll 1
-    for (int p = g.tid; p < nR; p += TPC) {
-        if (RX_OFF(p)) { OM[p] = 0.0; if (keep) { KF[p] = 0.0; KR[p] = 0.0; } continue; }
+    for (int q = g.tid; q < nLoop; q += TPC) {
+        const int p = RX_AT(q);
         const unsigned iw = S.info[p];
         const unsigned ty = V2_RTYPE(iw);
         double k = OM[p];
@@ -311,6 +321,7 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
         if (keep) { KF[p] = k; KR[p] = kr; }
     }
 #undef RX_OFF
+#undef RX_AT
     g.sync();
 }
 
@@ -403,12 +414,18 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
             double* D = WS(A) + 2 * nR;
             {
                 const unsigned long long* dp = cx->dterm;
+                const unsigned long long* MSKj = reinterpret_cast<const unsigned long long*>(WS(MSK));
 #pragma unroll 4
                 for (int k = t; k < nD; k += TPC) {
                     const unsigned long long wd = dp[k];
                     const unsigned kid = V2_T_K(wd);
-                    const double kk = KFR[(kid & 1u) * nR + (kid >> 1)];
-                    D[k] = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
+                    const unsigned pos = kid >> 1;
+                    double d = 0.0;
+                    if (!DAC || !((MSKj[pos >> 6] >> (pos & 63)) & 1ull)) {       // a disabled reaction contributes exact zeros
+                        const double kk = KFR[(kid & 1u) * nR + pos];
+                        d = ((kk * CC[V2_T_S1(wd)]) * CC[V2_T_S2(wd)]) * CC[V2_T_S3(wd)];
+                    }
+                    D[k] = d;
                 }
             }
             g.sync();
@@ -664,6 +681,11 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
     const int nW = (nR + 63) >> 6;
     g.sync();
     if (t <= nW) MSK[t] = 0ull;                       // every reaction takes part in the rate evaluation
+    {
+        unsigned short* RLw = reinterpret_cast<unsigned short*>(WS(RL) + 1);
+        for (int p = t; p < nR; p += TPC) RLw[p] = (unsigned short)p;
+        if (t == 0) reinterpret_cast<int*>(WS(RL))[0] = nR;
+    }
     const double T = y[nSp];
     const double lnT = log(T), invT = 1.0 / T;
     prepare(g, cx, base, y, T, lnT, true);
@@ -787,6 +809,19 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
         }
         const unsigned b = __ballot_sync(0xffffffffu, dis);
         if (g.lane == 0) reinterpret_cast<unsigned*>(MSK)[2 * c + g.warp] = b;
+        if (p < nR && dis) WS(OM)[p] = 0.0;           // stays zero: the sweeps only visit enabled reactions
+    }
+    g.sync();
+    // compacted list of the enabled reactions, ascending packed position: thread c lists the reactions of mask word c
+    if (t < nW) {
+        int basep = 0;
+        for (int c = 0; c < t; ++c) { const int hiBit = nR - c * 64 < 64 ? nR - c * 64 : 64; basep += hiBit - __popcll(MSK[c]); }
+        const int lim = nR - t * 64 < 64 ? nR - t * 64 : 64;
+        unsigned long long en = ~MSK[t];
+        if (lim < 64) en &= (1ull << lim) - 1ull;
+        unsigned short* RLw = reinterpret_cast<unsigned short*>(WS(RL) + 1);
+        while (en) { const int bpos = __ffsll((long long)en) - 1; en &= en - 1ull; RLw[basep++] = (unsigned short)(t * 64 + bpos); }
+        if (t == nW - 1) reinterpret_cast<int*>(WS(RL))[0] = basep;
     }
     g.sync();
     return __popcll(act);

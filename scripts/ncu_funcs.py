@@ -7,7 +7,7 @@ isamp = h.index("# Samples"); iinst = h.index("Instructions Executed")
 src = open(srcf).read().split('\n')
 starts = []
 for i, l in enumerate(src, 1):
-    m = re.match(r'^__device__ .*?(\w+)\(', l) or re.match(r'^__global__.*? (\w+)\(', l) or re.match(r'^struct (Grp)', l)
+    m = re.match(r'^(?:static )?__device__ .*?(\w+)\(', l) or re.match(r'^__global__.*? (\w+)\(', l) or re.match(r'^struct (Grp)', l)
     if m: starts.append((i, m.group(1)))
 def fn(ln):
     name = 'header'
