@@ -199,7 +199,7 @@ int configure_v2(lbchem_handle h) {
             int groups = (int)std::min<size_t>(lb_v3_max_groups(h->V2.tpc), (h->smemMax - fixed) / per3);
             if (const char* env = getenv("LBCHEM_GROUPS")) if (atoi(env) > 0) groups = std::min(groups, atoi(env));
             h->v3Groups = groups; h->v3Ws = ws;
-            h->scratchStride = (h->V2.nEnt + 11 * h->V2.nEqn + 1) & ~1;
+            h->scratchStride = (h->V2.nEnt + 14 * h->V2.nEqn + h->V2.nSp + 1) & ~1;   // sparse Jacobian, seulex table, owner-only vectors, dT column
             const size_t need = (size_t)h->nSM * groups * h->scratchStride * sizeof(double);
             if (need > h->scratchCap) {
                 if (h->dScratch) cudaFree(h->dScratch);

@@ -28,7 +28,7 @@ struct SMech {            // typed views into the staged blob
     const double *A, *beta, *Ta, *fall, *tcTab, *effVal;
     const unsigned* info; const unsigned long long *lpk, *rpk;
     const int *effPtr, *effSp, *spPtr, *rowPtr;
-    const unsigned* spList; const unsigned char* entCol;
+    const unsigned short* spList; const unsigned char* entCol;
 };
 
 __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned char* b) {
@@ -40,18 +40,20 @@ __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned c
     S.tcTab = P(double, oTcTab); S.effVal = P(double, oEffVal);
     S.info = P(unsigned, oInfo); S.lpk = P(unsigned long long, oLpk); S.rpk = P(unsigned long long, oRpk);
     S.effPtr = P(int, oEffPtr); S.effSp = P(int, oEffSp); S.spPtr = P(int, oSpPtr); S.rowPtr = P(int, oRowPtr);
-    S.spList = P(unsigned, oSpList); S.entCol = P(unsigned char, oEntCol);
+    S.spList = P(unsigned short, oSpList); S.entCol = P(unsigned char, oEntCol);
 #undef P
 }
 
-// cp coefficients and the matrix sparsity lists are read once per call by a few threads, the entropy polynomials once per
-// prepare() as one batch of independent coalesced loads: they stay in global memory (L2-resident) so that the
-// shared-memory copy of the mechanism is smaller and six cells fit per SM with an odd (conflict-free) matrix stride.
+// The thermodynamic polynomials (one batch of independent coalesced loads per prepare() / finish_derivatives()), the
+// Arrhenius beta / Ta (prefetched a round ahead), the fall-off parameters and the matrix sparsity lists stay in global
+// memory (L2-resident): the shared-memory copy of the mechanism shrinks from 28 KB to 13 KB for GRI, which is what lets a
+// seventh cell fit per SM.
 __device__ __forceinline__ void bind_cold(SMech& S, const V2Mech& M) {
     if (M.hotBytes >= M.blobBytes) return;
 #define PC(T, off) reinterpret_cast<const T*>(M.blob + M.off)
     S.cpLo = PC(double, oCpLo); S.cpHi = PC(double, oCpHi); S.rowPtr = PC(int, oRowPtr); S.entCol = PC(unsigned char, oEntCol);
-    S.sLo = PC(double, oSLo); S.sHi = PC(double, oSHi);
+    S.sLo = PC(double, oSLo); S.sHi = PC(double, oSHi); S.haLo = PC(double, oHaLo); S.haHi = PC(double, oHaHi);
+    S.beta = PC(double, oBeta); S.Ta = PC(double, oTa); S.fall = PC(double, oFall);
 #undef PC
 }
 
@@ -61,7 +63,7 @@ struct Ctx {
     SMech S;
     DevOpts O;
     int nEqn, nEnt, nFall, tbRows, lda, wsDoubles;
-    int oV, oCC, oGL, oGH, oME, oOM, oJT, oRD, oBS, oSTEP, oXCH, oXS, oCNT, oA, oMSK, oSX, oRL;
+    int oV, oCC, oGL, oGH, oME, oOM, oBS, oSTEP, oXCH, oXS, oCNT, oA, oMSK, oSX, oRL;
     const unsigned* jterm; const unsigned long long* dterm; int nD; const int* jthrEnt; const int* jthrN;
     const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
@@ -77,12 +79,14 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
         p += (M.nR + 63) / 64 + 1;            //   disabled-reaction bits (by packed position), then the active-species word
         c.oRL = p; p += 1 + (M.nR + 3) / 4;   //   int count + 16-bit list of the packed positions of the ENABLED reactions
     }
-    c.oV = p; p += 9 * N;
+    // vectors that other threads read (inputs of derivatives(), right-hand sides of lu_solve()) live here; the ones only
+    // their owner thread touches (seulex: f(y0), y0, scale; Rosenbrock34: y0, dydx0, dfdx) sit in the group's global
+    // scratch, and seul()'s column result travels in a register
+    c.oV = p; p += 5 * N;
     c.oCC = p; p += M.nSp + 1; c.oGL = p; p += M.nSp; c.oGH = p; p += M.nSp; c.oME = p; p += M.nEff;
-    c.oOM = p; p += M.nR; c.oJT = p; p += M.nSp;
-    c.oRD = p; p += N;
+    c.oOM = p; p += M.nR;
     c.oBS = p; p += N;
-    c.oSX = p; p += 24;                       // seulex: temp[12], dxOpt[12] (group-uniform step-size bookkeeping)
+    c.oSX = p; if (M.tbRows > 0) p += 24;     // seulex: temp[12], dxOpt[12] (group-uniform step-size bookkeeping)
     c.oSTEP = p; p += N + 1;                  // int STEP[N] (pivot column of each row), then int SPOF[N] (DAC: species of a compact column)
     c.lda = (M.nSp + 1) | 1;                  // odd (GRI: 55): one column read across the 16 rows of a half-warp touches 16 distinct 8-byte banks
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR + M.nD) ? M.nSp * c.lda : 2 * M.nR + M.nD;   // KF/KR and the Jacobian's D terms alias the matrix
@@ -92,6 +96,8 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
 // global scratch of this group: [nEnt] sparse Jacobian JS, then [tbRows x nEqn] seulex extrapolation table
 #define GS_JS (cx->scratch + (size_t)(blockIdx.x * cx->groups + threadIdx.x / TPC) * cx->scratchStride)
 #define GS_TB (GS_JS + cx->nEnt)
+#define GS_GV(i) (GS_JS + cx->nEnt + 11 * cx->nEqn + (i) * cx->nEqn)     /* owner-only vectors, i = 0..2 */
+#define GS_JT (GS_JS + cx->nEnt + 14 * cx->nEqn)                         /* d(dc/dt)/dT column of the Jacobian */
 #define VEC(i) (base + cx->oV + (i) * cx->nEqn)
 
 // ---- janaf polynomials (Horner forms identical to the oracle) -----------------------------------
@@ -127,8 +133,8 @@ __constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434
 constexpr int CTX_BYTES = 512;
 static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
 
-// threads per CTA: 384 whatever the group width (register file: 168 registers per thread)
-template <int TPC> struct Width { static constexpr int kMaxGroups = 384 / TPC; };
+// threads per CTA: seven 64-thread groups (144 registers per thread), else 384 threads (168 registers)
+template <int TPC> struct Width { static constexpr int kThreads = TPC == 64 ? 448 : 384; static constexpr int kMaxGroups = kThreads / TPC; static constexpr int kRegs = TPC == 64 ? 144 : 168; };
 
 // ================================================================================================
 // Everything below is written once for a group of TPC threads integrating one cell: TPC = 64 (two warps, named
@@ -213,8 +219,10 @@ static __device__ __forceinline__ void prepare(const Grp& g, const Ctx* cx, doub
     double cs = 0.0;
     if (t < nSp) {
         if (clamp) { const double c = fmax(y[t], 0.0); CC[t] = c; cs = c; }
-        WS(GL)[t] = jha(S.haLo + t, nSp, T) - T * js(S.sLo + t, nSp, T, lnT);
-        WS(GH)[t] = jha(S.haHi + t, nSp, T) - T * js(S.sHi + t, nSp, T, lnT);
+        // 24 independent coalesced loads from the L2-resident polynomials: all issued before the first use
+        const double gl = jha(S.haLo + t, nSp, T) - T * js(S.sLo + t, nSp, T, lnT);
+        const double gh = jha(S.haHi + t, nSp, T) - T * js(S.sHi + t, nSp, T, lnT);
+        WS(GL)[t] = gl; WS(GH)[t] = gh;
     }
     if (clamp) {
         if (t == nSp) CC[nSp] = 1.0;
@@ -248,12 +256,25 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
     const unsigned short* RL = reinterpret_cast<const unsigned short*>(WS(RL) + 1);
 #define RX_AT(q) (dac ? (int)RL[q] : (q))
     // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
+    // beta and Ta stream from global memory (L2): the next round's pair is in flight while this round's exp() runs; the
+    // fall-off parameters of pass (2) are fetched here as well, ahead of their use
+    double ff[7] = {0, 0, 0, 0, 0, 0, 0};
+    if (nFall > 0 && g.tid < nFall) {
+        const double* f = S.fall + 8 * V2_FALL(S.info[nR - nFall + g.tid]);
+#pragma unroll
+        for (int i = 0; i < 7; ++i) ff[i] = f[i];
+    }
+    {
+        int q = g.tid, p = 0; unsigned iw = 0; double be = 0.0, ta = 0.0;
+        if (q < nLoop) { p = RX_AT(q); iw = S.info[p]; if (V2_HASEXP(iw)) { be = S.beta[p]; ta = S.Ta[p]; } }
 #pragma unroll 1
-    for (int q = g.tid; q < nLoop; q += TPC) {
-        const int p = RX_AT(q);
-        double val = 1.0;
-        if (V2_HASEXP(S.info[p])) val = exp(fma(S.beta[p], lnT, -S.Ta[p] * invT));
-        OM[p] = val;
+        while (q < nLoop) {
+            const int qn = q + TPC;
+            int pn = 0; unsigned iwn = 0; double ben = 0.0, tan_ = 0.0;
+            if (qn < nLoop) { pn = RX_AT(qn); iwn = S.info[pn]; if (V2_HASEXP(iwn)) { ben = S.beta[pn]; tan_ = S.Ta[pn]; } }
+            OM[p] = V2_HASEXP(iw) ? exp(fma(be, lnT, -ta * invT)) : 1.0;
+            q = qn; p = pn; iw = iwn; be = ben; ta = tan_;
+        }
     }
     g.sync();
     // (2) fall-off reactions (sorted last): OM[p] <- blended rate constant
@@ -263,7 +284,16 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
             const int p = nR - nFall + q;
             if (RX_OFF(p)) continue;
             const unsigned iw = S.info[p];
-            const double* f = S.fall + 8 * V2_FALL(iw);
+            double fl[7];
+            if (q == g.tid) {
+#pragma unroll
+                for (int i = 0; i < 7; ++i) fl[i] = ff[i];
+            } else {
+                const double* fg = S.fall + 8 * V2_FALL(iw);
+#pragma unroll
+                for (int i = 0; i < 7; ++i) fl[i] = fg[i];
+            }
+            const double* f = fl;
             double k0 = f[0];
             if (fabs(f[1]) > LB_VSMALL || fabs(f[2]) > LB_VSMALL) k0 *= exp(fma(f[1], lnT, -f[2] * invT));
             const double kInf = S.A[p] * OM[p];
@@ -331,19 +361,17 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
 static __device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
     const int e = S.spPtr[i + 1];
-    int k = S.spPtr[i];
+    // lists are padded to multiples of four 16-bit entries (nu = 0 padding adds an exact zero): one 64-bit load per four terms
+    const unsigned long long* L = reinterpret_cast<const unsigned long long*>(S.spList);
 #pragma unroll 1
-    for (; k + 3 < e; k += 4) {
-        const unsigned u0 = S.spList[k], u1 = S.spList[k + 1], u2 = S.spList[k + 2], u3 = S.spList[k + 3];
-        a0 = fma((double)(int)(signed char)(u0 >> 16), om[u0 & 0xffffu], a0);
-        a1 = fma((double)(int)(signed char)(u1 >> 16), om[u1 & 0xffffu], a1);
-        a2 = fma((double)(int)(signed char)(u2 >> 16), om[u2 & 0xffffu], a2);
-        a3 = fma((double)(int)(signed char)(u3 >> 16), om[u3 & 0xffffu], a3);
-    }
-#pragma unroll 1
-    for (; k < e; ++k) {
-        const unsigned u = S.spList[k];
-        a0 = fma((double)(int)(signed char)(u >> 16), om[u & 0xffffu], a0);
+    for (int k = S.spPtr[i]; k < e; k += 4) {
+        const unsigned long long w = L[k >> 2];
+        const int u0 = (int)(short)(w & 0xffffu), u1 = (int)(short)((w >> 16) & 0xffffu), u2 = (int)(short)((w >> 32) & 0xffffu),
+                  u3 = (int)(short)(w >> 48);
+        a0 = fma((double)(u0 >> 12), om[u0 & 0xfff], a0);
+        a1 = fma((double)(u1 >> 12), om[u1 & 0xfff], a1);
+        a2 = fma((double)(u2 >> 12), om[u2 & 0xfff], a2);
+        a3 = fma((double)(u3 >> 12), om[u3 & 0xfff], a3);
     }
     return (a0 + a1) + (a2 + a3);
 }
@@ -404,8 +432,8 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
         if (pass == 0) {
             // species rates at (y, T): the dfdx slot (A.4 quirk) and, on request, the full derivatives() at the same state
             // (adaptiveSolver's dydx0: the reference evaluates it separately from the same rates)
-            const double d0 = (t < nSp && (cx->O.dfdxIsDcdt || dydt0)) ? gather_species(S, WS(OM), t) : 0.0;
-            if (t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? d0 : 0.0;
+            const double d0 = (t < nSp && ((dfdx && cx->O.dfdxIsDcdt) || dydt0)) ? gather_species(S, WS(OM), t) : 0.0;
+            if (dfdx && t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? d0 : 0.0;
             if (dydt0) finish_derivatives(g, cx, base, T, d0, dydt0);
             // (1) D terms: k * product of the other concentrations, one per (reaction, side, species), into the matrix
             //     region behind KF/KR; each is shared by every Jacobian row its reaction touches
@@ -457,7 +485,7 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
             }
         } else if (t < nSp) {
             const double d = gather_species(S, WS(OM), t);
-            if (pass == 1) dp = d; else WS(JT)[t] = 0.5 * (dp - d) / delta;
+            if (pass == 1) dp = d; else GS_JT[t] = 0.5 * (dp - d) / delta;
         }
         g.sync();
     }
@@ -502,7 +530,6 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
     const bool mine = t < nSp && cp.kept(t);
     const int cm = mine ? cp.index(t) : 0;
     double* A = WS(A);
-    double* RD = WS(RD);
     int* STEP = reinterpret_cast<int*>(WS(STEP));
     int* SPOF = STEP + N + (N & 1);               // DAC: species of compact column j
     double* XCH = WS(XCH);
@@ -539,7 +566,7 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
             for (; e < e1; ++e) { const int c = S.entCol[e]; if (cp.kept(c)) row[cp.index(c)] = -JS[e]; }
             SPOF[cm] = t;
         }
-        row[Ns] = -WS(JT)[t];
+        row[Ns] = -GS_JT[t];
         row[cm] += dg;
         big = 0.0;
 #pragma unroll 1
@@ -588,8 +615,8 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
         const int prw = reinterpret_cast<const int*>(sw + 1)[1];
         const double rd = sw[2];
         if (!done && cm == prw) {
-            done = true; STEP[t] = j; RD[j] = rd;
-            if (piv == 0.0) row[j] = LB_SMALL;
+            done = true; STEP[t] = j;
+            row[j] = rd;          // the diagonal slot of the pivot row keeps 1 / pivot (1 / SMALL for a zero pivot): all the solves need
         } else if (!done) {
             if (pos == j) pos = ppos;
             const double l = piv * rd;
@@ -634,7 +661,6 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
     const int Ns = cp.Ns;
     const bool sp = t < nSp && cp.kept(t);
     const double* row = WS(A) + (sp ? cp.index(t) : 0) * cp.ldc;
-    const double* RD = WS(RD);
     double* BS = WS(BS);
     const int* SPOF = reinterpret_cast<const int*>(WS(STEP)) + N + (N & 1);
     g.sync();
@@ -656,7 +682,7 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
     if (sp) bt = fma(-row[Ns], BS[Ns], bt);
 #pragma unroll 1
     for (int j = Ns - 1; j >= 0; --j) {
-        if (step == j) { const double v = bt * RD[j]; BS[j] = v; x[DAC ? SPOF[j] : j] = v; }
+        if (step == j) { const double v = bt * row[j]; BS[j] = v; x[DAC ? SPOF[j] : j] = v; }
         g.sync();
         if (sp && step < j) bt = fma(-row[j], BS[j], bt);
     }
@@ -694,7 +720,7 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
     double* NUM = WS(A);
     unsigned char* NB = reinterpret_cast<unsigned char*>(NUM + D[0]);     // neighbour B of each pair, after the numerators
     double *PA = VEC(1), *CA = VEC(2), *RV = VEC(3);
-    int* pairPtr = reinterpret_cast<int*>(VEC(5));
+    int* pairPtr = reinterpret_cast<int*>(VEC(4));                        // nSp + 1 ints; the search queue follows
     constexpr int PF = 8;                                                  // program words fetched ahead (L2 round trips)
     {
         // pair numerators: thread t owns a contiguous run of pairs, balanced by term count
@@ -751,7 +777,7 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
     }
     g.sync();
     if (g.warp == 0) {
-        unsigned char* Q = reinterpret_cast<unsigned char*>(VEC(4));
+        unsigned char* Q = reinterpret_cast<unsigned char*>(pairPtr + ((nSp + 2) & ~1));
         const double tol = __hiloint2double(D[17], D[16]);
         unsigned long long act = 0ull;
         int head = 0, tail = 0;
@@ -843,7 +869,9 @@ static __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const C
                  b3 = 25.0 / 108.0, b4 = 125.0 / 108.0, e1 = 34.0 / 108.0, e2 = 7.0 / 36.0, e3 = 0, e4 = 125.0 / 108.0,
                  gamma = 1.0 / 2.0, c1X = 1.0 / 2.0, c2X = -3.0 / 2.0, c3X = 121.0 / 50.0, c4X = 29.0 / 250.0;
     const int t = g.tid, N = cx->nEqn;
-    double *Y0 = VEC(0), *Y = VEC(1), *D0 = VEC(2), *DX = VEC(3), *K1 = VEC(4), *K2 = VEC(5), *K3 = VEC(6), *K4 = VEC(7), *DY = VEC(8);
+    double *Y = VEC(0), *K1 = VEC(1), *K2 = VEC(2), *K3 = VEC(3), *K4 = VEC(4);
+    double* DY = K4;      // derivatives() output of stages 2-3; stage 4 turns it into k4's right-hand side element by element, in place
+    const double *Y0 = GS_GV(0), *D0 = GS_GV(1), *DX = GS_GV(2);     // read by their owner thread only
     const int st = lu_factor<DAC>(cx, base, 1.0 / (gamma * dx));
     if (st) { cs.fail = st; return 0.0; }
     if (t == 0) CNT(CNT_JAC)++;    // algorithmic count: the reference evaluates the Jacobian in every attempt
@@ -853,7 +881,7 @@ static __device__ __forceinline__ double rosenbrock34_step(const Grp& g, const C
             if (t < N) Y[t] = (s == 1) ? Y0[t] + a21 * K1[t] : Y0[t] + a31 * K1[t] + a32 * K2[t];
             derivatives<DAC>(cx, base, Y, DY);
         }
-        double* K = VEC(4 + s);
+        double* K = VEC(1 + s);
         if (t < N) {
             double r;
             if (s == 0) r = D0[t] + dx * c1X * DX[t];
@@ -881,7 +909,7 @@ static __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* c
     const int t = g.tid, N = cx->nEqn;
     double dx = dxTry, err = 0.0;
     // dydx0 and the Jacobian are both evaluated at (y0, T0)
-    jacobian<DAC>(cx, base, VEC(0), VEC(3), VEC(2));
+    jacobian<DAC>(cx, base, GS_GV(0), GS_GV(2), GS_GV(1));
     if (t == 0) CNT(CNT_JAC)--;                 // counted per attempt in rosenbrock34_step
     do {
         if (t == 0) CNT(CNT_ATTEMPTS)++;
@@ -896,7 +924,7 @@ static __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* c
     } while (err > 1);
     x += dx;
     g.sync();
-    if (t < N) VEC(0)[t] = VEC(1)[t];
+    if (t < N) GS_GV(0)[t] = VEC(0)[t];
     g.sync();
     if (err > pow(maxScale / safeScale, -1.0 / alphaInc))
         dxTry = fmin(fmax(safeScale * pow(err, -alphaInc), minScale), maxScale) * dx;
@@ -908,11 +936,12 @@ static __device__ __forceinline__ void adaptive_solve(const Grp& g, const Ctx* c
 // `phase` keeps derivatives() and lu_solve() at one call site each: phase 1 = the stability check of the
 // second sub-step (solves dyc), phase 0 = the regular Euler increment (solves dy).
 template <bool DAC>
-static __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k) {
+static __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double* base, Cell& cs, double dxTot, int k, double& yOut) {
     const int t = g.tid, N = cx->nEqn;
     const int nSteps = c_nSeq[k];
     const double dx = dxTot / nSteps;
-    double *y0 = VEC(4), *scale = VEC(5), *yOut = VEC(6), *dy = VEC(7), *yT = VEC(1), *f = VEC(8), *dyc = VEC(2);
+    double *dy = VEC(3), *yT = VEC(1), *f = VEC(4), *dyc = VEC(2);
+    double *f0 = GS_GV(0), *y0 = GS_GV(1), *scale = GS_GV(2);         // each element is read and written by its owner thread only
     const int st = lu_factor<DAC>(cx, base, 1 / dx);
     if (st) { cs.fail = st; return false; }
     bool ok = true;
@@ -926,11 +955,11 @@ static __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double*
             if (it == 0 && cs.f0valid) {
                 // f(y0) is the same for every column and every retry of this step: the reference re-evaluates it,
                 // we keep it in V3 (counted as an evaluation all the same)
-                if (t < N) f[t] = VEC(3)[t];
+                if (t < N) f[t] = f0[t];
                 if (t == 0) CNT(CNT_RHS)++;
             } else {
                 derivatives<DAC>(cx, base, it == 0 ? y0 : yT, f);
-                if (it == 0) { if (t < N) VEC(3)[t] = f[t]; cs.f0valid = 1; }
+                if (it == 0) { if (t < N) f0[t] = f[t]; cs.f0valid = 1; }
             }
             if (it == 1 && k <= 1) phase = 1;
         }
@@ -964,7 +993,7 @@ static __device__ __forceinline__ bool seul(const Grp& g, const Ctx* cx, double*
             ++it;
         }
     }
-    if (ok) { if (t < N) yOut[t] = yT[t] + dy[t]; }
+    if (ok && t < N) yOut = yT[t] + dy[t];
     g.sync();
     return ok;
 }
@@ -984,7 +1013,7 @@ static __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx,
                  kFactor1 = 0.7, kFactor2 = 0.9;
     const double absTol = O.absTol, relTol = O.relTol;
     const double jacRedo = fmin(1e-4, relTol);
-    double *y = VEC(0), *y0 = VEC(4), *scale = VEC(5), *ySeq = VEC(6), *tb = GS_TB;
+    double *y = VEC(0), *y0 = GS_GV(1), *scale = GS_GV(2), *tb = GS_TB;
     // temp / dxOpt are group-uniform: one copy in the workspace (every thread writes the same value; reads follow a group
     // barrier of the column loop), not 48 registers per thread
     double* temp = WS(SX); double* dxOpt = temp + 12;
@@ -1004,7 +1033,7 @@ static __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx,
     bool jacUpdated = false;
     if (cs.theta > jacRedo) {
         // the Jacobian's first rate sweep is at (y0, T0): it also yields f(y0) for the first Euler sub-step of every column
-        jacobian<DAC>(cx, base, y, VEC(8), VEC(3));
+        jacobian<DAC>(cx, base, y, nullptr, GS_GV(0));
         if (t == 0) CNT(CNT_RHS)--;            // counted when seul() consumes it
         cs.f0valid = 1;
         jacUpdated = true;
@@ -1022,14 +1051,15 @@ static __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx,
         double errOld = 0;
 #pragma unroll 1
         for (k = 0; k <= cs.kTarg + 1; ++k) {
-            const bool success = seul<DAC>(g, cx, base, cs, dx, k);
+            double ySeqT = 0.0;                      // this thread's element of the column result
+            const bool success = seul<DAC>(g, cx, base, cs, dx, k, ySeqT);
             if (cs.fail) return;
             if (!success) { step.reject = 1; dxNew = fabs(dx) * stepFactor5; break; }
             double s = 0.0;
             if (t < N) {
-                if (k == 0) y[t] = ySeq[t];
+                if (k == 0) y[t] = ySeqT;
                 else {
-                    tb[(k - 1) * N + t] = ySeq[t];
+                    tb[(k - 1) * N + t] = ySeqT;
                     for (int j = k - 1; j > 0; --j)
                         tb[(j - 1) * N + t] = tb[j * N + t] + seulex_coeff(k, j) * (tb[j * N + t] - tb[(j - 1) * N + t]);
                     const double yi = tb[t] + seulex_coeff(k, 0) * (tb[t] - y[t]);
@@ -1089,7 +1119,7 @@ static __device__ __forceinline__ void seulex_solve(const Grp& g, const Ctx* cx,
             step.prevReject = 1;
             if (!jacUpdated) {
                 cs.theta = 2.0 * jacRedo;
-                if (cs.theta > jacRedo && !jacUpdated) { jacobian<DAC>(cx, base, y, VEC(8), nullptr); jacUpdated = true; }
+                if (cs.theta > jacRedo && !jacUpdated) { jacobian<DAC>(cx, base, y, nullptr, nullptr); jacUpdated = true; }
             }
         }
     }
@@ -1212,7 +1242,7 @@ static __device__ __forceinline__ void integrate_body(const V2Mech& M, const Dev
         if (t == 0) CNT(CNT_NODE) = cx->nEqn;
         int status;
         double Tend = T0;
-        double* y = VEC(0);
+        double* y = (SOLVER == LBCHEM_SOLVER_SEULEX) ? VEC(0) : GS_GV(0);      // the state vector the solver advances
         if (T0 > O.Treact) {
             if (t < nSp) y[t] = rho * Yp[(size_t)t * ldy + cell] / S.W[t];
             if (t == nSp) y[nSp] = T0;
@@ -1374,16 +1404,16 @@ static __device__ __forceinline__ void probe_body(const V2Mech& M, const DevOpts
             const double* KF = WS(A);
             for (int p = t; p < 2 * nR; p += TPC) o[p] = KF[p];
         } else {
-            jacobian<false>(cx, base, y, VEC(8), nullptr);
+            jacobian<false>(cx, base, y, VEC(2), nullptr);
             if (kind == LBCHEM_PROBE_JAC) {
-                if (t < N) o[t] = VEC(8)[t];
+                if (t < N) o[t] = VEC(2)[t];
                 double* J = o + N;
                 for (int k = t; k < N * N; k += TPC) J[k] = 0.0;
                 g.sync();
                 if (t < nSp) {
                     const double* JS = GS_JS;
                     for (int e = S.rowPtr[t]; e < S.rowPtr[t + 1]; ++e) J[t * N + S.entCol[e]] = JS[e];
-                    J[t * N + nSp] = WS(JT)[t];
+                    J[t * N + nSp] = GS_JT[t];
                 }
             } else {                                   // LBCHEM_PROBE_JAC_LUSOLVE: x = (dg I - J(y))^-1 b
                 const double dg = x[N];
@@ -1401,15 +1431,15 @@ static __device__ __forceinline__ void probe_body(const V2Mech& M, const DevOpts
 };   // struct K<TPC>
 
 template <int TPC, int SOLVER, bool DAC>
-__global__ void __launch_bounds__(384, 1) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
+__global__ void __maxnreg__(Width<TPC>::kRegs) integrate_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles) {
     K<TPC>::template integrate_body<SOLVER, DAC>(M, O, B, wsDoubles);
 }
 template <int TPC>
-__global__ void __launch_bounds__(384, 1) tc_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, double* tcOut) {
+__global__ void __launch_bounds__(Width<TPC>::kThreads, 1) tc_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, double* tcOut) {
     K<TPC>::tc_body(M, O, B, wsDoubles, tcOut);
 }
 template <int TPC>
-__global__ void __launch_bounds__(384, 1) probe_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, int kind, int nItems,
+__global__ void __launch_bounds__(Width<TPC>::kThreads, 1) probe_v3_kernel(V2Mech M, DevOpts O, BatchArgs B, int wsDoubles, int kind, int nItems,
                                                           const double* in, int inStride, double* out, int outStride) {
     K<TPC>::probe_body(M, O, B, wsDoubles, kind, nItems, in, inStride, out, outStride);
 }
@@ -1429,7 +1459,7 @@ int lb_v3_workspace(V2Mech& M, int solver, double relTol, double absTol) {
 
 bool lb_v3_supported(const V2Mech& M) { return M.nEqn <= 64 && M.nEqn >= 3 && M.tpc >= M.nEqn; }
 int lb_v3_ctx_bytes() { return v3::CTX_BYTES; }
-int lb_v3_max_groups(int tpc) { return 384 / tpc; }
+int lb_v3_max_groups(int tpc) { return tpc == 64 ? 7 : 384 / tpc; }
 
 namespace {
 template <int TPC, int SOLVER, bool DAC>

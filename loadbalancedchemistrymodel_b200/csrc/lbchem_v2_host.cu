@@ -209,17 +209,12 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
     while (tcTab.size() < 8) tcTab.push_back(0.0);
 
     Blob B;
-    {
-        const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
-        const int haI[6] = {4, 3, 2, 1, 0, 5}; const double haD[6] = {5, 4, 3, 2, 1, 1};
-        M.oW = B.add(std::vector<double>(m->W, m->W + nSp));
-        M.oTc = B.add(std::vector<double>(m->Tcommon, m->Tcommon + nSp));
-        M.oHaLo = B.add(soa2(m->janaf_low, nSp, haI, haD, 6)); M.oHaHi = B.add(soa2(m->janaf_high, nSp, haI, haD, 6));
-    }
-    M.oA = B.add(A); M.oBeta = B.add(beta); M.oTa = B.add(Ta); M.oInfo = B.add(info);
+    M.oW = B.add(std::vector<double>(m->W, m->W + nSp));
+    M.oTc = B.add(std::vector<double>(m->Tcommon, m->Tcommon + nSp));
+    M.oA = B.add(A); M.oInfo = B.add(info);
     M.oLpk = B.add(lpk); M.oRpk = B.add(rpk);
     if (fall.empty()) fall.push_back(0.0);
-    M.oFall = B.add(fall); M.oTcTab = B.add(tcTab);
+    M.oTcTab = B.add(tcTab);
 
     // sparse third-body efficiencies: M_e = sum_i c_i + sum_{eff != 1} (eff - 1) c_i
     {
@@ -235,17 +230,25 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         M.oEffPtr = B.add(effPtr); M.oEffSp = B.add(effSp); M.oEffVal = B.add(effVal);
     }
 
-    // omega gather lists: species-major, ORIGINAL reaction order, lhs before rhs (the reference's accumulation order)
+    // omega gather lists: species-major, ORIGINAL reaction order, lhs before rhs (the reference's accumulation order);
+    // 16-bit entries (packed position | signed nu << 12), every species' list padded to a multiple of four entries
+    // (nu = 0) so that the kernel reads four entries with one 64-bit load
     {
-        std::vector<int> spPtr(nSp + 1, 0); std::vector<uint32_t> spList;
-        std::vector<std::vector<uint32_t>> L(nSp);
+        if (nR > 4095) return 1;
+        std::vector<int> spPtr(nSp + 1, 0); std::vector<uint16_t> spList;
+        std::vector<std::vector<uint16_t>> L(nSp);
         for (int r = 0; r < nR; ++r) {
             for (int k = m->lhs_ptr[r]; k < m->lhs_ptr[r + 1]; ++k)
-                L[m->lhs_species[k]].push_back((uint32_t)posOf[r] | ((uint32_t)(uint8_t)(int8_t)(-(int)m->lhs_nu[k]) << 16));
+                L[m->lhs_species[k]].push_back((uint16_t)((unsigned)posOf[r] | (((unsigned)(-(int)m->lhs_nu[k]) & 15u) << 12)));
             for (int k = m->rhs_ptr[r]; k < m->rhs_ptr[r + 1]; ++k)
-                L[m->rhs_species[k]].push_back((uint32_t)posOf[r] | ((uint32_t)(uint8_t)(int8_t)((int)m->rhs_nu[k]) << 16));
+                L[m->rhs_species[k]].push_back((uint16_t)((unsigned)posOf[r] | (((unsigned)((int)m->rhs_nu[k]) & 15u) << 12)));
         }
-        for (int i = 0; i < nSp; ++i) { spList.insert(spList.end(), L[i].begin(), L[i].end()); spPtr[i + 1] = (int)spList.size(); }
+        for (int i = 0; i < nSp; ++i) {
+            while (L[i].size() % 4) L[i].push_back(0);
+            spList.insert(spList.end(), L[i].begin(), L[i].end());
+            spPtr[i + 1] = (int)spList.size();
+        }
+        if (spList.empty()) spList.assign(4, 0);
         M.oSpPtr = B.add(spPtr); M.oSpList = B.add(spList);
     }
 
@@ -303,13 +306,20 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         }
         while (row < N) rowPtr[++row] = (int)entCol.size();
     }
-    // cold tail of the blob (the v3 kernel leaves it in global memory): cp and entropy polynomials, matrix sparsity lists
+    // cold tail of the blob (the v3 kernel leaves it in global memory, L2-resident): everything that is read as a batch of
+    // independent coalesced loads once per call -- the enthalpy / entropy / cp polynomials (prepare, finish_derivatives),
+    // the Arrhenius beta and Ta (prefetched one round ahead by the rate sweep), the fall-off parameters (prefetched before
+    // the first pass) -- and the matrix sparsity lists. What stays in shared memory is what every reaction of every sweep
+    // reads with data-dependent addresses.
     M.hotBytes = (int)B.b.size();
     {
         const int cpI[5] = {0, 1, 2, 3, 4}; const double cpD[5] = {1, 1, 1, 1, 1};
+        const int haI[6] = {4, 3, 2, 1, 0, 5}; const double haD[6] = {5, 4, 3, 2, 1, 1};
         const int sI[6] = {4, 3, 2, 1, 0, 6};  const double sD[6] = {4, 3, 2, 1, 1, 1};
+        M.oHaLo = B.add(soa2(m->janaf_low, nSp, haI, haD, 6)); M.oHaHi = B.add(soa2(m->janaf_high, nSp, haI, haD, 6));
         M.oCpLo = B.add(soa2(m->janaf_low, nSp, cpI, cpD, 5)); M.oCpHi = B.add(soa2(m->janaf_high, nSp, cpI, cpD, 5));
         M.oSLo = B.add(soa2(m->janaf_low, nSp, sI, sD, 6));    M.oSHi = B.add(soa2(m->janaf_high, nSp, sI, sD, 6));
+        M.oBeta = B.add(beta); M.oTa = B.add(Ta); M.oFall = B.add(fall);
     }
     M.oRowPtr = B.add(rowPtr);
     if (entCol.empty()) entCol.push_back(0);

@@ -1,0 +1,31 @@
+#!/bin/bash
+mkdir -p gpurun_out
+run() { tag=$1; shift
+  env LBCHEM_VERBOSE=1 "$@" python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu-baseline --no-imbalanced $ARGS > gpurun_out/s_$tag.json 2> gpurun_out/s_$tag.err
+  python - <<PY
+import json
+try:
+    d=json.load(open("gpurun_out/s_$tag.json"))
+    print("$tag", round(d["value"]), "cells/s  ms", round(d["ms_per_step"],2), "failed", d["failed_cells"], "frac", round(d["roofline"]["frac"],4))
+except Exception as e:
+    print("$tag FAILED", e); print(open("gpurun_out/s_$tag.err").read()[-800:])
+PY
+  grep -m1 "v3 kernel" gpurun_out/s_$tag.err
+}
+timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/r02_g_pytest.log 2>&1
+echo "pytest exit $?" >> gpurun_out/r02_g_pytest.log
+tail -4 gpurun_out/r02_g_pytest.log
+ARGS="--workload gri_uniform --solver seulex --cells 200000"
+run g7_s X=1
+run g6_s LBCHEM_GROUPS=6
+ARGS="--workload gri_uniform --solver Rosenbrock34 --cells 200000"
+run g7_r X=1
+run g6_r LBCHEM_GROUPS=6
+ARGS="--workload gri_dac --solver seulex --cells 400000"
+run dac3 X=1
+ARGS="--workload gri_tiled --solver seulex --cells 400000"
+run nodac3 X=1
+ARGS="--workload h2_air --solver Rosenbrock34 --cells 1000000"
+run h2_3 X=1
+ARGS="--workload ch4_mixing --solver Rosenbrock34 --cells 1000000"
+run ch4_3 X=1
