@@ -209,6 +209,11 @@ int configure_v2(lbchem_handle h) {
             }
             h->v3Smem = fixed + per3 * groups;
             CK(lb_v3_configure(h->V2.tpc, o.solver, h->v3Smem));
+            if (getenv("LBCHEM_VERBOSE") && h->V2.tpc == 64) {
+                int r = 0, mt = 0, ss = 0;
+                lb_v3_kernel_info(o.solver, &r, &mt, &ss);
+                fprintf(stderr, "[lbchem] v3 kernel attributes: %d registers, maxThreadsPerBlock %d, static smem %d B\n", r, mt, ss);
+            }
             if (getenv("LBCHEM_VERBOSE"))
                 fprintf(stderr, "[lbchem] v3 kernel: %d threads per cell, %d cells per CTA, %d B workspace per cell, %d B mechanism in smem, %zu B dynamic smem\n",
                         h->V2.tpc, groups, (int)per3, h->V2.hotBytes, h->v3Smem);

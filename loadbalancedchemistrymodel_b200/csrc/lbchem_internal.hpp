@@ -21,6 +21,7 @@ bool lb_v3_supported(const V2Mech& M);
 int lb_v3_ctx_bytes();
 cudaError_t lb_v3_configure(int tpc, int solver, size_t smemBytes);
 int lb_v3_max_groups(int tpc);
+cudaError_t lb_v3_kernel_info(int solver, int* regs, int* maxThreads, int* staticSmem);
 cudaError_t lb_v3_launch(int tpc, int solver, int grid, int groups, size_t smemBytes, int wsDoubles, const V2Mech& M, const DevOpts& O,
                          const BatchArgs& B, cudaStream_t s);
 size_t lb_work_doubles(const DevMech& M, int solver);

@@ -133,8 +133,9 @@ __constant__ double c_cpu[12] = {10, 15, 22, 33, 48, 71, 102, 149, 212, 307, 434
 constexpr int CTX_BYTES = 512;
 static_assert(sizeof(Ctx) <= CTX_BYTES, "Ctx grew: raise CTX_BYTES");
 
-// threads per CTA: seven 64-thread groups (144 registers per thread), else 384 threads (168 registers)
-template <int TPC> struct Width { static constexpr int kThreads = TPC == 64 ? 448 : 384; static constexpr int kMaxGroups = kThreads / TPC; static constexpr int kRegs = TPC == 64 ? 144 : 168; };
+// threads per CTA: seven 64-thread groups = 14 warps, i.e. four warps on two of the SM's sub-partitions: 16384 / (4 x 32) =
+// 128 registers per thread at most; else 384 threads (168 registers)
+template <int TPC> struct Width { static constexpr int kThreads = TPC == 64 ? 448 : 384; static constexpr int kMaxGroups = kThreads / TPC; static constexpr int kRegs = TPC == 64 ? 128 : 168; };
 
 // ================================================================================================
 // Everything below is written once for a group of TPC threads integrating one cell: TPC = 64 (two warps, named
@@ -1484,6 +1485,15 @@ cudaError_t launch_tpc(int solver, int grid, int groups, size_t smemBytes, int w
     return cudaGetLastError();
 }
 }  // namespace
+
+// registers per thread, the kernel's own thread limit and its static shared memory (LBCHEM_VERBOSE diagnostics)
+cudaError_t lb_v3_kernel_info(int solver, int* regs, int* maxThreads, int* staticSmem) {
+    cudaFuncAttributes a{};
+    cudaError_t e = solver == LBCHEM_SOLVER_SEULEX ? cudaFuncGetAttributes(&a, v3::integrate_v3_kernel<64, LBCHEM_SOLVER_SEULEX, false>)
+                                                   : cudaFuncGetAttributes(&a, v3::integrate_v3_kernel<64, LBCHEM_SOLVER_ROSENBROCK34, false>);
+    *regs = a.numRegs; *maxThreads = a.maxThreadsPerBlock; *staticSmem = (int)a.sharedSizeBytes;
+    return e;
+}
 
 cudaError_t lb_v3_configure(int tpc, int solver, size_t smemBytes) {
     switch (tpc) {
