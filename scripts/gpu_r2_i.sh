@@ -10,22 +10,19 @@ try:
 except Exception as e:
     print("$tag FAILED", e); print(open("gpurun_out/s_$tag.err").read()[-800:])
 PY
-  grep -m1 "v3 kernel" gpurun_out/s_$tag.err
 }
-timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/r02_g_pytest.log 2>&1
-echo "pytest exit $?" >> gpurun_out/r02_g_pytest.log
-tail -4 gpurun_out/r02_g_pytest.log
+timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/r02_i_pytest.log 2>&1
+echo "pytest exit $?" >> gpurun_out/r02_i_pytest.log
+tail -4 gpurun_out/r02_i_pytest.log
 ARGS="--workload gri_uniform --solver seulex --cells 200000"
-run g7_s X=1
-run g6_s LBCHEM_GROUPS=6
+run i_s X=1
 ARGS="--workload gri_uniform --solver Rosenbrock34 --cells 200000"
-run g7_r X=1
-run g6_r LBCHEM_GROUPS=6
+run i_r X=1
 ARGS="--workload gri_dac --solver seulex --cells 400000"
-run dac3 X=1
+run i_dac X=1
 ARGS="--workload gri_tiled --solver seulex --cells 400000"
-run nodac3 X=1
+run i_nodac X=1
 ARGS="--workload h2_air --solver Rosenbrock34 --cells 1000000"
-run h2_3 X=1
+run i_h2 X=1
 ARGS="--workload ch4_mixing --solver Rosenbrock34 --cells 1000000"
-run ch4_3 X=1
+run i_ch4 X=1
