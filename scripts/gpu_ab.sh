@@ -11,9 +11,9 @@ except Exception as e:
     print("$tag FAILED", e); print(open("gpurun_out/s_$tag.err").read()[-800:])
 PY
 }
-timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/r02_i_pytest.log 2>&1
-echo "pytest exit $?" >> gpurun_out/r02_i_pytest.log
-tail -4 gpurun_out/r02_i_pytest.log
+timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/ab_pytest.log 2>&1
+echo "pytest exit $?" >> gpurun_out/ab_pytest.log
+tail -4 gpurun_out/ab_pytest.log
 ARGS="--workload gri_uniform --solver seulex --cells 200000"
 run i_s X=1
 ARGS="--workload gri_uniform --solver Rosenbrock34 --cells 200000"
