@@ -580,116 +580,72 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
     if (done && t < N) STEP[t] = -1;              // T, p and removed species: diagonal rows, solved in closed form
     if (t == 0) WS(XS)[1] = 1.0 / dg;
     int par = 1;      // exchange buffer, toggled per pivot column
-    // Right-looking BLOCKED elimination, panels of NB pivot columns. Inside a panel the rank-1 updates touch the panel's
-    // own columns only; the columns to the right receive the panel's NB updates in one pass, each element through the same
-    // chain of fused multiply-adds, in the same order, as column-by-column elimination would apply (bit-identical factors),
-    // but with ONE load and ONE store of the element per panel instead of per column, and the pivot rows read as broadcasts.
-    constexpr int NB = 8;
-    int* PR = reinterpret_cast<int*>(WS(BS));     // rows that became the panel's pivot rows (BS is free until the solves)
 #pragma unroll 1
-    for (int jb = 0; jb < Ns; jb += NB) {
-        const int je = jb + NB < Ns ? jb + NB : Ns;
-        const int nbk = je - jb;
-        // ---- the panel: pivot vote, multipliers, updates restricted to columns < je
-#pragma unroll 1
-        for (int j = jb; j < je; ++j) {
-            par ^= 1;
-            const double piv = done ? 0.0 : row[j];
-            const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
-            const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
-            // one reduction on the top 32 bits of the key decides the warp's candidate whenever that maximum is unique
-            // (the common case); ties in the top half fall through to the exact 64-bit + position comparison
-            const unsigned mh = __reduce_max_sync(g.mask, hi);
-            const bool c1 = hi == mh;
-            bool win = c1;
-            if (__popc(__ballot_sync(g.mask, c1)) != 1) {
-                const unsigned ml = __reduce_max_sync(g.mask, c1 ? lo : 0u);
-                const bool c2 = c1 && lo == ml;
-                const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
-                const unsigned mp = __reduce_max_sync(g.mask, pp);
-                win = c2 && pp == mp;
-            }
-            if (win) {
-                double* slot = XCH + (g.warp * 2 + par) * 4;
-                slot[0] = __longlong_as_double((long long)key);
-                reinterpret_cast<int*>(slot + 1)[0] = pos;
-                reinterpret_cast<int*>(slot + 1)[1] = cm;
-                slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
-            }
-            g.sync();
-            const double* s0 = XCH + (0 * 2 + par) * 4;
-            const double* s1 = XCH + (1 * 2 + par) * 4;
-            const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
-            const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
-            const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
-            const double* sw = (Grp::kTwoWarps && (k1 > k0 || (k1 == k0 && p1 > p0))) ? s1 : s0;   // one warp: its candidate is the pivot
-            const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
-            const int prw = reinterpret_cast<const int*>(sw + 1)[1];
-            const double rd = sw[2];
-            if (!done && cm == prw) {
-                done = true; STEP[t] = j;
-                row[j] = rd;          // the diagonal slot of the pivot row keeps 1 / pivot (1 / SMALL for a zero pivot): all the solves need
-                PR[j - jb] = cm;
-            } else if (!done) {
-                if (pos == j) pos = ppos;
-                const double l = piv * rd;
-                row[j] = l;
-                const double* __restrict__ prow = A + prw * ldc;
-#pragma unroll 1
-                for (int k = j + 1; k < je; ++k) row[k] = fma(-l, prow[k], row[k]);
-            }
+    for (int j = 0; j < Ns; ++j) {
+        par ^= 1;
+        const double piv = done ? 0.0 : row[j];
+        const unsigned long long key = done ? 0ull : (unsigned long long)__double_as_longlong(vv * fabs(piv)) + 1ull;
+        const unsigned hi = (unsigned)(key >> 32), lo = (unsigned)key;
+        // one reduction on the top 32 bits of the key decides the warp's candidate whenever that maximum is unique
+        // (the common case); ties in the top half fall through to the exact 64-bit + position comparison
+        const unsigned mh = __reduce_max_sync(g.mask, hi);
+        const bool c1 = hi == mh;
+        bool win = c1;
+        if (__popc(__ballot_sync(g.mask, c1)) != 1) {
+            const unsigned ml = __reduce_max_sync(g.mask, c1 ? lo : 0u);
+            const bool c2 = c1 && lo == ml;
+            const unsigned pp = c2 ? (unsigned)pos + 1u : 0u;
+            const unsigned mp = __reduce_max_sync(g.mask, pp);
+            win = c2 && pp == mp;
         }
-        g.sync();                                 // the panel's multipliers and pivot rows are in place
-        const int ntrail = Ns + 1 - je;           // columns je .. Ns (the temperature column is always there)
-        // ---- (A) the panel's pivot rows, by COLUMNS: thread tau finishes column je + tau of all nbk pivot rows in registers
-        //      (pivot row q still lacks the updates of the pivots 0 .. q-1 of this panel)
-#pragma unroll 1
-        for (int kk = t; kk < ntrail; kk += TPC) {
-            const int k = je + kk;
-            double u[NB];
-#pragma unroll
-            for (int q = 0; q < NB; ++q) {
-                if (q < nbk) {
-                    double* pr = A + PR[q] * ldc;
-                    double a = pr[k];
-#pragma unroll
-                    for (int q2 = 0; q2 < q; ++q2) a = fma(-pr[jb + q2], u[q2], a);
-                    u[q] = a;
-                    if (q > 0) pr[k] = a;
-                }
-            }
+        if (win) {
+            double* slot = XCH + (g.warp * 2 + par) * 4;
+            slot[0] = __longlong_as_double((long long)key);
+            reinterpret_cast<int*>(slot + 1)[0] = pos;
+            reinterpret_cast<int*>(slot + 1)[1] = cm;
+            slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
         }
         g.sync();
-        // ---- (B) every row still in play: its elements right of the panel take the panel's nbk updates, eight elements at a
-        //      time (eight independent chains), the pivot rows read as broadcasts
-        if (!done) {
-            double l[NB]; int po[NB];
-#pragma unroll
-            for (int q = 0; q < NB; ++q) { l[q] = q < nbk ? row[jb + q] : 0.0; po[q] = q < nbk ? PR[q] * ldc : 0; }
-            int k = je;
+        const double* s0 = XCH + (0 * 2 + par) * 4;
+        const double* s1 = XCH + (1 * 2 + par) * 4;
+        const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
+        const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
+        const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
+        const double* sw = (Grp::kTwoWarps && (k1 > k0 || (k1 == k0 && p1 > p0))) ? s1 : s0;   // one warp: its candidate is the pivot
+        const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
+        const int prw = reinterpret_cast<const int*>(sw + 1)[1];
+        const double rd = sw[2];
+        if (!done && cm == prw) {
+            done = true; STEP[t] = j;
+            row[j] = rd;          // the diagonal slot of the pivot row keeps 1 / pivot (1 / SMALL for a zero pivot): all the solves need
+        } else if (!done) {
+            if (pos == j) pos = ppos;
+            const double l = piv * rd;
+            row[j] = l;
+            const double* __restrict__ prow = A + prw * ldc;
+            double* __restrict__ mine_ = row;
+            int k = j + 1;
+            // batches of eight, then four: all loads first, so the stores of one batch never wait behind its loads
 #pragma unroll 1
             for (; k + 7 <= Ns; k += 8) {
-                double a[8];
-#pragma unroll
-                for (int i = 0; i < 8; ++i) a[i] = row[k + i];
-#pragma unroll
-                for (int q = 0; q < NB; ++q) {
-                    if (q < nbk) {
-                        const double* __restrict__ uq = A + po[q] + k;
-#pragma unroll
-                        for (int i = 0; i < 8; ++i) a[i] = fma(-l[q], uq[i], a[i]);
-                    }
-                }
-#pragma unroll
-                for (int i = 0; i < 8; ++i) row[k + i] = a[i];
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double p4 = prow[k + 4], p5 = prow[k + 5], p6 = prow[k + 6], p7 = prow[k + 7];
+                const double r0 = mine_[k], r1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                const double r4 = mine_[k + 4], r5 = mine_[k + 5], r6 = mine_[k + 6], r7 = mine_[k + 7];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, r1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
+                mine_[k + 4] = fma(-l, p4, r4); mine_[k + 5] = fma(-l, p5, r5);
+                mine_[k + 6] = fma(-l, p6, r6); mine_[k + 7] = fma(-l, p7, r7);
             }
 #pragma unroll 1
-            for (; k <= Ns; ++k) {
-                double a = row[k];
-#pragma unroll
-                for (int q = 0; q < NB; ++q) if (q < nbk) a = fma(-l[q], A[po[q] + k], a);
-                row[k] = a;
+            for (; k + 3 <= Ns; k += 4) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double r0 = mine_[k], r1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, r1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
             }
+#pragma unroll 1
+            for (; k <= Ns; ++k) mine_[k] = fma(-l, prow[k], mine_[k]);
         }
     }
     if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
