@@ -161,7 +161,7 @@ struct Grp {
     // group barrier (also orders the group's shared and global memory accesses): a named barrier for two warps, a
     // (sub-)warp barrier otherwise
     __device__ __forceinline__ void sync() const {
-        if (kTwoWarps) asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "r"(TPC) : "memory");
+        if (kTwoWarps) asm volatile("bar.sync %0, %1;" ::"r"(gid + 1), "n"(TPC) : "memory");
         else __syncwarp(mask);
     }
     // Reductions write slot `s` (0..3). Two reductions with no barrier in between must use different slots. Every
@@ -606,15 +606,19 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
             slot[2] = 1.0 / ((piv == 0.0) ? LB_SMALL : piv);
         }
         g.sync();
+        // both warps' candidates are read in one go (no second, dependent round trip through shared memory)
         const double* s0 = XCH + (0 * 2 + par) * 4;
         const double* s1 = XCH + (1 * 2 + par) * 4;
         const unsigned long long k0 = (unsigned long long)__double_as_longlong(s0[0]);
-        const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
-        const int p0 = reinterpret_cast<const int*>(s0 + 1)[0], p1 = reinterpret_cast<const int*>(s1 + 1)[0];
-        const double* sw = (Grp::kTwoWarps && (k1 > k0 || (k1 == k0 && p1 > p0))) ? s1 : s0;   // one warp: its candidate is the pivot
-        const int ppos = reinterpret_cast<const int*>(sw + 1)[0];
-        const int prw = reinterpret_cast<const int*>(sw + 1)[1];
-        const double rd = sw[2];
+        const int2 i0 = *reinterpret_cast<const int2*>(s0 + 1);
+        const double rd0 = s0[2];
+        int ppos = i0.x, prw = i0.y; double rd = rd0;
+        if (Grp::kTwoWarps) {
+            const unsigned long long k1 = (unsigned long long)__double_as_longlong(s1[0]);
+            const int2 i1 = *reinterpret_cast<const int2*>(s1 + 1);
+            const double rd1 = s1[2];
+            if (k1 > k0 || (k1 == k0 && i1.x > i0.x)) { ppos = i1.x; prw = i1.y; rd = rd1; }
+        }
         if (!done && cm == prw) {
             done = true; STEP[t] = j;
             row[j] = rd;          // the diagonal slot of the pivot row keeps 1 / pivot (1 / SMALL for a zero pivot): all the solves need
