@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--no-pageable", action="store_true")
     ap.add_argument("--imbalanced-cells", type=int, default=1_000_000, help="cells in TOTAL of the imbalanced batch")
     ap.add_argument("--imbalanced-steps", type=int, default=2)
+    ap.add_argument("--dac", action="store_true", help="switch the DAC reduction on for any GRI workload (as --workload gri_dac does for the tiled fixture)")
     ap.add_argument("--carry-dtchem", action="store_true",
                     help="carry deltaTChem from step to step like the model does between flow steps (default for gri_skewed)")
     return ap.parse_args()
@@ -115,7 +116,7 @@ def cpu_oracle_rate(args, n_sample, nthreads, steps=1, warmup=0):
     s, atol, rtol = SOLVERS[args.solver]
     mech, Y, T, p, rho = make_workload(args.workload, n_sample, rank=0)
     om = O.OracleModel(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol))
-    if args.workload == "gri_dac":
+    if args.workload == "gri_dac" or getattr(args, "dac", False):
         om.set_reduction(DAC_TOL, dac_initial_set(mech))
     for _ in range(warmup):
         om.solve_batch(Y, T, p, rho, 1e-6, 1e-7, nthreads=nthreads)
@@ -255,7 +256,7 @@ def cpu_plan_baseline(ranks, cells_per_rank):
             "how": "oracle threads as MPI ranks; plan applied to the measured per-cell wall times (makespan = slowest rank)"}
 
 
-def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north_star", cpu_plan=False):
+def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north_star", cpu_plan=False, economy=False):
     """The load-balancing experiment: `total_cells` in TOTAL (strong scaling), the hot 10 % contiguous at the start of the
     global index space (rank 0 holds them), deltaTChem carried from step to step, integrated once without and once
     with the redistribution (same lbchem_lb entry point, balance off / on). seulex 1e-12 / 1e-3 over deltaT = 1e-4 is the
@@ -286,12 +287,18 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
            "tdac": bool(dac), "cost_model": "work units 9 nLU + nSolve + 3 nRHS + 12 nJac (lbchem_options.cost_model = 1)",
            "deltaTChem": "1e-07 on step 0 (the firstTime_ local step), then carried"}
     results = {}
+    shared = LoadBalancedChemistryModel(chem, tdac=dac, balance=False) if economy else None
+    carried = dtc0
     for mode in ("unbalanced", "balanced"):
-        model = LoadBalancedChemistryModel(chem, tdac=dac, balance=(mode == "balanced"))
+        # economy (the 4 M-cell config): ONE model -- step 0 local, step 1 timed with the exchange off, then the exchange is
+        # switched on: one planning step, then the timed balanced steps; the expensive local step 0 is not repeated
+        model = shared if economy else LoadBalancedChemistryModel(chem, tdac=dac, balance=(mode == "balanced"))
+        if economy and mode == "balanced":
+            model.set_balance(True)
         out = {"RR": torch.empty((nSp, n), dtype=torch.float64, device=dev), "T": torch.empty(n, dtype=torch.float64, device=dev),
                "cost": torch.empty(n, dtype=torch.float64, device=dev), "status": torch.empty(n, dtype=torch.int32, device=dev)}
-        dtc = dtc0
-        nwarm = 2                                          # step 0 is local in both; the balanced model plans on step 1
+        dtc = carried if economy else dtc0
+        nwarm = 2 if not economy else 1                    # step 0 is local in both; the balanced model plans on step 1
         times, moved, nbytes, kms = [], 0, 0, []
         for it in range(nwarm + steps):
             R.barrier()
@@ -323,10 +330,12 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
                 _ = float(ho["cost"].sum())
             R.barrier()
             results["e2e_s"] = R.reduce((time.perf_counter() - t0) / steps)
-        model.close()
+        carried = dtc
+        if not economy or mode == "balanced":
+            model.close()
     ub, bl = results["unbalanced"], results["balanced"]
     same = bool(torch.equal(ub["RR"], bl["RR"]) and torch.equal(ub["dtc"], bl["dtc"]) and torch.equal(ub["cost"], bl["cost"]))
-    same = R.reduce(0.0 if same else 1.0) == 0.0
+    same = (R.reduce(0.0 if same else 1.0) == 0.0) if not economy else None     # economy: the two results are different flow steps
     loads = None
     if world > 1:
         import torch.distributed as dist
@@ -392,7 +401,7 @@ def run_b200(args):
     mech, Y, T, p, rho = make_workload(args.workload, n, rank, world)
     nSp = mech.n_species
     chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol), device=local)
-    if args.workload == "gri_dac":
+    if args.workload == "gri_dac" or args.dac:
         chem.set_reduction(DAC_TOL, dac_initial_set(mech))
 
     def pinned(a):
@@ -500,7 +509,7 @@ def run_b200(args):
         imbalanced = run_imbalanced(R, rank, local, args.imbalanced_cells, steps=args.imbalanced_steps,
                                     cpu_plan=(world == 1 and not args.no_cpu_baseline))
         if world == 8 and not args.no_extra_configs:
-            extra["config4_gri_skewed_4M"] = run_imbalanced(R, rank, local, 4_000_000, steps=1, label="BASELINE config 4")
+            extra["config4_gri_skewed_4M"] = run_imbalanced(R, rank, local, 4_000_000, steps=1, label="BASELINE config 4", economy=True)
             extra["config5_gri_dac_1M"] = run_imbalanced(R, rank, local, 1_000_000, dac=True, steps=3, label="BASELINE config 5")
 
     if rank == 0:

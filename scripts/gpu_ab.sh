@@ -26,3 +26,8 @@ ARGS="--workload h2_air --solver Rosenbrock34 --cells 1000000"
 run i_h2 X=1
 ARGS="--workload ch4_mixing --solver Rosenbrock34 --cells 1000000"
 run i_ch4 X=1
+# where DAC pays: hot cells only (config 3 input) and cold cells only, with and without the reduction
+ARGS="--workload gri_uniform --solver seulex --cells 200000 --dac"
+run hot_dac X=1
+ARGS="--workload gri_uniform --solver seulex --cells 200000"
+run hot_nodac LBCHEM_GROUPS=6
