@@ -257,6 +257,27 @@ int lbchem_cells_to_send_device(lbchem_handle h, const double* cell_cost, int64_
                                 int64_t* bounds, void* stream);
 
 /*
+ * The same cellsToSend search for callers that cannot allocate (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc). No counterpart in the reference.
+ *   - allocates NOTHING: no cudaMalloc / cudaFree / cudaHostAlloc, no allocating library routine; it only enqueues kernels
+ *     (and one cudaMemsetAsync when n == 0) on `stream` of the CURRENT device and returns without synchronising;
+ *   - cell_cost[n], targets[nT] (inputs) and bounds[nT + 1] (output) are all DEVICE arrays of the current device;
+ *   - its two-level prefix structure (tile sums, exclusive tile prefix: 3 doubles per 1024 cells) lives in one file-scope
+ *     device array of the library, sized for LBCHEM_NOALLOC_MAX_CELLS cells (about 96 KiB; every GPU that loads the
+ *     library holds it until the process exits). n beyond that, or nT beyond LBCHEM_NOALLOC_MAX_TARGETS, is rejected
+ *     with LBCHEM_E_INVALID and a message in err (if given; always NUL-terminated);
+ *   - every call on one GPU shares that array: calls that overlap on the GPU (different streams, no ordering) RACE.
+ *     Order them on one stream or with events. Nothing in the array has to start at zero: every element a call reads is
+ *     written earlier in the same call, so the previous call's contents never show.
+ * The first call on each device resolves the array's device address (cudaGetSymbolAddress; not an allocation): make
+ * one call per device before starting a graph capture. Results are bit-identical to lbchem_cells_to_send_device.
+ */
+#define LBCHEM_NOALLOC_MAX_CELLS   4194304   /* 4 Mi cells = 4096 tiles of 1024 */
+#define LBCHEM_NOALLOC_MAX_TARGETS 1024
+int lbchem_cells_to_send_noalloc(const double* cell_cost, int64_t n, const double* targets, int32_t nT, int64_t* bounds,
+                                 void* stream, char* err, int32_t err_len);
+
+/*
  * FP64-pipe peak of the device (DFMA micro-benchmark, ~ms_target milliseconds): the roofline denominator of
  * the chemistry kernels (bench.py; MEASURED_PEAKS.json carries no FP64 figure). device < 0: current device.
  */

@@ -175,6 +175,7 @@ def load_library(path: Path | None = None) -> C.CDLL:
     lib.lbchem_cells_to_send.argtypes = [_dp, C.c_int32, C.c_double, C.c_int32]
     lib.lbchem_cells_to_send.restype = C.c_int32
     lib.lbchem_cells_to_send_device.argtypes = [H, C.c_void_p, C.c_int64, _dp, C.c_int32, C.POINTER(C.c_int64), C.c_void_p]
+    lib.lbchem_cells_to_send_noalloc.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_int32, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int32]
     declare_lb(lib)
     L = C.c_void_p
     lib.lbchem_lb_nccl_unique_id.argtypes = [C.c_void_p]
@@ -226,10 +227,24 @@ def lb_options(update_iter=0, min_fraction=0.02, tdac=False, balance=True) -> Lb
 EXPORTED_SYMBOLS = (
     "lbchem_version lbchem_default_options lbchem_create lbchem_destroy lbchem_set_options lbchem_get_options "
     "lbchem_last_error lbchem_solve_batch lbchem_solve_batch_host lbchem_solve_batch_indexed lbchem_get_stats lbchem_balance_plan "
-    "lbchem_cells_to_send lbchem_cells_to_send_device lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc "
+    "lbchem_cells_to_send lbchem_cells_to_send_device lbchem_cells_to_send_noalloc lbchem_probe lbchem_fp64_peak lbchem_set_reduction lbchem_get_active_species lbchem_qdot lbchem_tc "
     "lbchem_lb_default_options lbchem_lb_nccl_unique_id lbchem_lb_create_nccl lbchem_lb_create_transport lbchem_lb_create_loopback "
     "lbchem_lb_set_options lbchem_lb_destroy lbchem_lb_last_error lbchem_lb_solve lbchem_lb_solve_host lbchem_lb_get_info lbchem_lb_get_plan"
 ).split()
+
+
+NOALLOC_MAX_CELLS = 4194304     # LBCHEM_NOALLOC_MAX_CELLS
+NOALLOC_MAX_TARGETS = 1024      # LBCHEM_NOALLOC_MAX_TARGETS
+
+
+def cells_to_send_noalloc(cost_ptr, n, targets_ptr, nT, bounds_ptr, stream=0, lib=None):
+    """``lbchem_cells_to_send_noalloc``: raw DEVICE pointers in and out, nothing allocated on either side of the boundary
+    (this wrapper only builds ctypes scalars and a 256-byte host message buffer). Returns (rc, message)."""
+    lib = lib or load_library()
+    err = C.create_string_buffer(256)
+    rc = lib.lbchem_cells_to_send_noalloc(C.c_void_p(cost_ptr), int(n), C.c_void_p(targets_ptr), int(nT), C.c_void_p(bounds_ptr),
+                                          C.c_void_p(stream), err, 256)
+    return int(rc), err.value.decode()
 
 
 def balance_plan(cost, cells=None, min_fraction=0.02, tdac=False, lib=None):

@@ -6,6 +6,9 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <atomic>
+#include <cstdio>
+
 #include "lbchem_internal.hpp"
 #include "lbchem_lb_capi.hpp"
 
@@ -426,6 +429,68 @@ int lbchem_cells_to_send_device(lbchem_handle h, const double* cell_cost, int64_
     if (be.bounds(cell_cost, n, targets, nT, b.data(), stream)) return lb_fail(h, LBCHEM_E_CUDA, be.err);
     for (int k = 0; k <= nT; ++k) bounds[k] = b[k];
     return LBCHEM_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// cellsToSend without any allocation (include/lbchem.h: lbchem_cells_to_send_noalloc; no counterpart in the reference).
+// Same three kernels as CudaBackend::reduce / bounds; their scratch is the
+// file-scope device array below instead of cudaMalloc'ed buffers. In HOST code `g_noalloc_scratch` is only a stand-in
+// for the symbol: the device address comes from cudaGetSymbolAddress, once per device, with that device current.
+// ------------------------------------------------------------------------------------------------
+constexpr int kNoallocTiles = LBCHEM_NOALLOC_MAX_CELLS / kTile;                 // 4096
+constexpr int kNoallocDoubles = 3 * kNoallocTiles + 8;                          // tileSum | tileMin | tileExcl[+1] | out[2]
+static_assert(LBCHEM_NOALLOC_MAX_CELLS % kTile == 0, "the cell limit is a whole number of tiles");
+static __device__ __align__(256) double g_noalloc_scratch[kNoallocDoubles];
+constexpr int kNoallocMaxDev = 64;
+static std::atomic<double*> g_noalloc_ptr[kNoallocMaxDev];                        // zero-initialised: not resolved yet
+
+static int noalloc_fail(char* err, int32_t len, const char* fmt, long long a, long long b) {
+    if (err && len > 0) snprintf(err, (size_t)len, fmt, a, b);
+    return LBCHEM_E_INVALID;
+}
+
+int lbchem_cells_to_send_noalloc(const double* cell_cost, int64_t n, const double* targets, int32_t nT, int64_t* bounds,
+                                 void* stream, char* err, int32_t err_len) {
+    if (err && err_len > 0) err[0] = 0;
+    if (!targets || !bounds || nT < 0 || n < 0 || (n > 0 && !cell_cost))
+        return noalloc_fail(err, err_len, "lbchem_cells_to_send_noalloc: null pointer or negative size (n = %lld, nT = %lld)", (long long)n, nT);
+    if (n > LBCHEM_NOALLOC_MAX_CELLS)
+        return noalloc_fail(err, err_len, "lbchem_cells_to_send_noalloc: n = %lld exceeds LBCHEM_NOALLOC_MAX_CELLS = %lld "
+                            "(the static scratch is sized for that; use lbchem_cells_to_send_device)", (long long)n, LBCHEM_NOALLOC_MAX_CELLS);
+    if (nT > LBCHEM_NOALLOC_MAX_TARGETS)
+        return noalloc_fail(err, err_len, "lbchem_cells_to_send_noalloc: nT = %lld exceeds LBCHEM_NOALLOC_MAX_TARGETS = %lld", nT, LBCHEM_NOALLOC_MAX_TARGETS);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    auto cuda_fail = [&](cudaError_t e, const char* what) {
+        if (err && err_len > 0) snprintf(err, (size_t)err_len, "lbchem_cells_to_send_noalloc: %s: %s", what, cudaGetErrorString(e));
+        return LBCHEM_E_CUDA;
+    };
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice");
+    if (dev < 0 || dev >= kNoallocMaxDev) return noalloc_fail(err, err_len, "lbchem_cells_to_send_noalloc: device ordinal %lld not below %lld", dev, kNoallocMaxDev);
+    double* base = g_noalloc_ptr[dev].load(std::memory_order_acquire);
+    if (!base) {                                  // set-up, once per device (racing first calls resolve the same address)
+        e = cudaGetSymbolAddress(reinterpret_cast<void**>(&base), g_noalloc_scratch);
+        if (e != cudaSuccess || !base) return cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_scratch)");
+        g_noalloc_ptr[dev].store(base, std::memory_order_release);
+    }
+    if (n == 0) {                                 // the sequential loop returns n = 0 for every target
+        e = cudaMemsetAsync(bounds, 0, (size_t)(nT + 1) * sizeof(int64_t), s);
+        return e == cudaSuccess ? LBCHEM_OK : cuda_fail(e, "cudaMemsetAsync");
+    }
+    double* tileSum = base;
+    double* tileMin = base + kNoallocTiles;
+    double* tileExcl = base + 2 * kNoallocTiles;  // nb + 1 entries
+    double* out = base + 3 * kNoallocTiles + 1;   // total, min (unused by the caller)
+    const int nb = (int)((n + kTile - 1) / kTile);
+    // every entry read below (tileSum / tileMin [0, nb), tileExcl [0, nb]) is written by the two kernels before: nothing
+    // of the previous call's contents is ever read, so nothing needs clearing
+    lb_tile_reduce<<<nb, 256, 0, s>>>(cell_cost, cell_cost, n, tileSum, tileMin);
+    lb_tile_scan<<<1, 1024, 0, s>>>(tileSum, tileMin, nb, tileExcl, out);
+    static_assert(sizeof(long long) == sizeof(int64_t), "bounds are 64-bit");
+    lb_bounds<<<1, 1024, 0, s>>>(cell_cost, n, tileExcl, nb, targets, nT, reinterpret_cast<long long*>(bounds));
+    e = cudaGetLastError();
+    return e == cudaSuccess ? LBCHEM_OK : cuda_fail(e, "kernel launch");
 }
 
 int lbchem_lb_destroy(lbchem_lb lb) {
