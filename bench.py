@@ -537,8 +537,9 @@ def run_b200(args):
         roofline = {
             "bound": "fp64", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak, "traffic": traffic,
             "traffic_source": traffic_src,
-            "kernel": ("v3::integrate_v3_kernel<solver> (one launch per shard; lbchem_kernels_v3.cu)" if nSp + 2 > 16 and s != "EulerImplicit"
-                       else "integrate_kernel<8 or 16 threads per cell> (general kernel, sub-warp groups; lbchem_kernels.cu)"), "kernel_ms": k_ms,
+            "kernel": (f"integrate_v3_kernel<{min(w for w in (8, 16, 32, 64) if w >= nSp + 2)} threads per cell, solver> "
+                       "(one launch per shard; lbchem_kernels_v3.cu)" if s != "EulerImplicit"
+                       else "integrate_kernel<8 threads per cell> (general kernel, sub-warp groups; lbchem_kernels.cu)"), "kernel_ms": k_ms,
             "peak_source": "DFMA micro-benchmark (lbchem_fp64_peak) run in this process after the timed region; MEASURED_PEAKS.json has no FP64 entry",
             "flops_per_cell": flops / max(1, st["n_cells"]), "flop_model": "SURVEY 8(d): nLU*2/3 n^3 + nSolve*2 n^2 + nRHS*F_rhs + nJac*F_jac, transcendentals x20, reference-algorithm counts"
                           + (" at the FULL system size n = 55 (upper bound: the reduced systems are smaller)" if args.workload == "gri_dac" else ""),
