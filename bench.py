@@ -39,6 +39,9 @@ SOLVERS = {"seulex": ("seulex", 1e-12, 1e-1), "Rosenbrock34": ("Rosenbrock34", 1
 MECH_OF = {"h2_air": "H2/O2 sub-mechanism of GRI-3.0 (10 species, 29 reactions)", "ch4_mixing": "1-step CH4 (5 species, 1 reaction)"}
 
 
+PIVOTING = 1      # lbchem_options.pivoting of every handle this run creates (--pivoting)
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -57,6 +60,8 @@ def parse():
     ap.add_argument("--imbalanced-cells", type=int, default=1_000_000, help="cells in TOTAL of the imbalanced batch")
     ap.add_argument("--imbalanced-steps", type=int, default=2)
     ap.add_argument("--dac", action="store_true", help="switch the DAC reduction on for any GRI workload (as --workload gri_dac does for the tiled fixture)")
+    ap.add_argument("--pivoting", type=int, default=1, choices=[0, 1, 2],
+                    help="lbchem_options.pivoting: 1 = diagonal pivots with the growth test and the reference's rule as fallback (default), 0 = the reference's rule on every matrix")
     ap.add_argument("--carry-dtchem", action="store_true",
                     help="carry deltaTChem from step to step like the model does between flow steps (default for gri_skewed)")
     return ap.parse_args()
@@ -101,6 +106,9 @@ def config_dict(args, n_gpus, extra=None):
         "mechanism": MECH_OF.get(args.workload, "GRI-3.0"), "cells_per_gpu": args.cells, "solver": s, "absTol": atol, "relTol": rtol,
         "deltaT": 1e-6, "deltaTChem0": 1e-7, "parallelism": (f"cells sharded over {n_gpus} GPUs; every step through lbchem_lb_solve (C++ driver: all-gather of the cost, bit-exact plan, device cellsToSend, NCCL p2p of field-major row slices, one two-segment launch)" if n_gpus > 1 else "1 GPU, one persistent kernel per step"),
         "l2": "inputs (464 B/cell x cells) larger than L2; no flush needed",
+        "pivoting": {1: "diagonal pivots, growth test, reference rule as fallback (lbchem_options.pivoting = 1, default)",
+                     0: "the reference's partial pivoting on every matrix (lbchem_options.pivoting = 0)",
+                     2: "test hook: diagonal path always rejected"}[args.pivoting],
     }
     if args.carry_dtchem or args.workload == "gri_skewed":
         cfg["deltaTChem0"] = "1e-07 on the first (warm-up) step, then carried from step to step as the model does"
@@ -275,7 +283,7 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
         mech, Y, T, p, rho = W.gri_skewed(n, rank=rank, world=world)
         solver, atol, rtol, dT = IMB["solver"], IMB["absTol"], IMB["relTol"], IMB["deltaT"]
     nSp = mech.n_species
-    opts = capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol, cost_model=1)
+    opts = capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol, cost_model=1, pivoting=PIVOTING)
     chem = capi.Chemistry(mech, opts, device=local)
     if dac:
         chem.set_reduction(DAC_TOL, dac_initial_set(mech))
@@ -352,7 +360,7 @@ def run_imbalanced(R, rank, local, total_cells, dac=False, steps=2, label="north
     if rank == 0 and not dac:
         ns = 2000
         mech2, Ys, Ts, ps, rhos = W.gri_skewed(2 * ns, hot_fraction=0.5, seed=77)
-        c2 = capi.Chemistry(mech2, capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol), device=local)
+        c2 = capi.Chemistry(mech2, capi.default_options(solver=solver, abs_tol=atol, rel_tol=rtol, pivoting=PIVOTING), device=local)
         r1 = c2.solve_host(Ys, Ts, ps, rhos, dT, W.DELTA_T_CHEM0)
         r2 = c2.solve_host(Ys, Ts, ps, rhos, dT, r1["deltaTChem"])
         c2.close()
@@ -400,7 +408,7 @@ def run_b200(args):
     n = args.cells
     mech, Y, T, p, rho = make_workload(args.workload, n, rank, world)
     nSp = mech.n_species
-    chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol), device=local)
+    chem = capi.Chemistry(mech, capi.default_options(solver=s, abs_tol=atol, rel_tol=rtol, pivoting=args.pivoting), device=local)
     if args.workload == "gri_dac" or args.dac:
         chem.set_reduction(DAC_TOL, dac_initial_set(mech))
 
@@ -573,7 +581,9 @@ def run_b200(args):
 
 
 def main():
+    global PIVOTING
     args = parse()
+    PIVOTING = args.pivoting
     # Libraries (NCCL's version banner, torchrun notices) may write to stdout; the contract is ONE JSON line there.
     # Everything but the final line goes to stderr.
     sys.stdout.flush()

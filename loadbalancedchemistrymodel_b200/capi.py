@@ -46,6 +46,7 @@ class Options(C.Structure):
         ("eq_rate_limiter", C.c_int32), ("dfdx_is_dcdt", C.c_int32), ("gas_constant", C.c_double),
         ("kc_floor", C.c_double), ("threads_per_cell", C.c_int32), ("sort_by_cost", C.c_int32),
         ("seulex_errold_max", C.c_int32), ("cost_model", C.c_int32),
+        ("pivoting", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
@@ -91,7 +92,7 @@ def default_options(**kw) -> Options:
     o = Options(
         solver=SOLVER_ROSENBROCK34, max_steps=10000, abs_tol=1e-15, rel_tol=1e-4, Treact=0.0,
         deltaTChemMax=1e15, cTauChem=1.0, eq_rate_limiter=0, dfdx_is_dcdt=1, gas_constant=RR_DEFAULT,
-        kc_floor=1e-6, threads_per_cell=0, sort_by_cost=0, seulex_errold_max=0, cost_model=0,
+        kc_floor=1e-6, threads_per_cell=0, sort_by_cost=0, seulex_errold_max=0, cost_model=0, pivoting=1,
     )
     for k, v in kw.items():
         if k == "solver" and isinstance(v, str):

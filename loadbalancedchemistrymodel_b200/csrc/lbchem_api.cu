@@ -263,7 +263,7 @@ void set_devopts(lbchem_handle h) {
     d.solver = o.solver; d.maxSteps = o.max_steps; d.absTol = o.abs_tol; d.relTol = o.rel_tol; d.Treact = o.Treact;
     d.deltaTChemMax = o.deltaTChemMax; d.cTauChem = o.cTauChem; d.eqRateLimiter = o.eq_rate_limiter;
     d.dfdxIsDcdt = o.dfdx_is_dcdt; d.RR = o.gas_constant; d.kcFloor = o.kc_floor;
-    d.seulexErrOldMax = o.seulex_errold_max;
+    d.seulexErrOldMax = o.seulex_errold_max; d.pivoting = o.pivoting;
 }
 
 }  // namespace
@@ -293,6 +293,7 @@ void lbchem_default_options(lbchem_options* o) {
     o->sort_by_cost = 0;
     o->seulex_errold_max = 0;
     o->cost_model = 0;
+    o->pivoting = 1;
 }
 
 int lbchem_create(const lbchem_mech_desc* mech, int device, lbchem_handle* out) {

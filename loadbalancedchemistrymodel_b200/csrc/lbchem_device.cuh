@@ -57,7 +57,7 @@ struct DevOpts {
     double absTol, relTol, Treact, deltaTChemMax, cTauChem;
     int eqRateLimiter, dfdxIsDcdt;
     double RR, kcFloor;
-    int seulexErrOldMax, pad_;
+    int seulexErrOldMax, pivoting;   // pivoting: lbchem_options.pivoting (compact-code kernel)
 };
 
 // one contiguous block of cells, field-major (the reference's cell list after pack: baseDataContainer.H:85-117)

@@ -68,7 +68,7 @@ struct Ctx {
     const int* dac;                               // DAC program, null when reduction is off
     double* scratch; int scratchStride, groups;   // per-group global (L2-resident) scratch: sparse Jacobian, seulex table
 };
-enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N, CNT_NODE = 7 };   // CNT_NODE: equations of the ODE system (NsDAC_+2 when reduced)
+enum { CNT_STEPS = 0, CNT_ATTEMPTS, CNT_JAC, CNT_LU, CNT_SOLVE, CNT_RHS, CNT_N, CNT_DIAG = 6, CNT_NODE = 7 };   // CNT_DIAG: the factors in the workspace come from the diagonal-pivot path; CNT_NODE: equations of the ODE system (NsDAC_+2 when reduced)
 
 __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     const int N = M.nEqn;
@@ -520,24 +520,11 @@ struct Compact {
     __device__ __forceinline__ int index(int sp) const { return DAC ? __popcll(act & ((1ull << sp) - 1ull)) : sp; }
 };
 
-// Build the matrix from the sparse Jacobian and factorise it: LUDecompose (A.10) with implicit row scaling and
-// partial pivoting. Rows never move: `pos` is the index the row would have in the reference's physically swapped
-// matrix (drives its tie rule: the LAST maximal row wins), STEP[t] the column at which row t became the pivot row.
-template <bool DAC>
-static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
-    const Grp g(base);
+// row t of dg I - J from the sparse store into the shared matrix (compacted when DAC); returns max |row| when asked for
+template <bool DAC, bool WANT_BIG>
+static __device__ __forceinline__ double lu_build(const Ctx* cx, double* base, const Compact<DAC>& cp, double* row, int* SPOF, bool mine, int cm, double dg) {
     const SMech& S = cx->S;
-    const int nSp = S.nSp, t = g.tid, N = cx->nEqn;
-    const Compact<DAC> cp(cx, base);
-    const int Ns = cp.Ns, ldc = cp.ldc;
-    const bool mine = t < nSp && cp.kept(t);
-    const int cm = mine ? cp.index(t) : 0;
-    double* A = WS(A);
-    int* STEP = reinterpret_cast<int*>(WS(STEP));
-    int* SPOF = STEP + N + (N & 1);               // DAC: species of compact column j
-    double* XCH = WS(XCH);
-    double* row = A + cm * ldc;
-    g.sync();
+    const int t = threadIdx.x % TPC, Ns = cp.Ns;
     double big = fabs(dg);
     if (mine) {
 #pragma unroll 1
@@ -571,10 +558,124 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
         }
         row[Ns] = -GS_JT[t];
         row[cm] += dg;
-        big = 0.0;
+        if (WANT_BIG) {
+            big = 0.0;
 #pragma unroll 1
-        for (int k = 0; k <= Ns; ++k) big = fmax(big, fabs(row[k]));
+            for (int k = 0; k <= Ns; ++k) big = fmax(big, fabs(row[k]));
+        }
     }
+    return big;
+}
+
+// Factorisation with DIAGONAL pivots (lbchem_options.pivoting = 1, the default): no vote, no exchange. Returns true when
+// it is accepted -- every multiplier below 2^10; the reference's choice is the diagonal in 96 % of the columns of the GRI
+// flame workloads and the largest multiplier met there is 2.0 -- else the caller factorises the matrix again with the
+// reference's rule. pivoting = 2 rejects always (test hook of that fallback).
+template <bool DAC>
+static __device__ __noinline__ bool lu_factor_diag(const Ctx* cx, double* base, double dg) {
+    const Grp g(base);
+    const int nSp = cx->S.nSp, t = g.tid, N = cx->nEqn;
+    const Compact<DAC> cp(cx, base);
+    const int Ns = cp.Ns, ldc = cp.ldc;
+    const bool mine = t < nSp && cp.kept(t);
+    const int cm = mine ? cp.index(t) : 0;
+    double* A = WS(A);
+    int* STEP = reinterpret_cast<int*>(WS(STEP));
+    int* SPOF = STEP + N + (N & 1);               // DAC: species of compact column j
+    double* row = A + cm * ldc;
+    g.sync();
+    lu_build<DAC, false>(cx, base, cp, row, SPOF, mine, cm, dg);
+    // ---- diagonal pivots. Row j is final after step j - 1; its owner leaves 1 / pivot in the diagonal slot (what
+    // lu_solve needs as well) before the barrier of step j. The reciprocal is computed by EVERY lane on a harmless
+    // operand (1.0 except in the owner of row j + 1), right after the first element of the row update, so that its
+    // dependent chain runs under the loads and FMAs of the rest of the row instead of serialising one warp.
+    if (mine && cm == 0) { const double d = row[0]; row[0] = 1.0 / ((d == 0.0) ? LB_SMALL : d); }
+    if (t < N) STEP[t] = mine ? cm : -1;
+    if (t == 0) WS(XS)[1] = 1.0 / dg;
+    double gmax = 0.0;
+#pragma unroll 1
+    for (int j = 0; j < Ns; ++j) {
+        g.sync();
+        if (mine && cm > j) {
+            const double* __restrict__ prow = A + j * ldc;
+            double* __restrict__ mine_ = row;
+            const double l = mine_[j] * prow[j];
+            int k = j + 1;
+            const double r1 = fma(-l, prow[k], mine_[k]);
+            const bool nxt = cm == k;
+            const double den = nxt ? ((r1 == 0.0) ? LB_SMALL : r1) : 1.0;
+            double rc;
+            mine_[j] = l; gmax = fmax(gmax, fabs(l));
+            ++k;
+            if (k + 7 <= Ns) {
+                // first batch of the row, peeled: the Newton chain of the reciprocal (the one 1.0 / den compiles to, without
+                // its range check: a pivot outside 2^+-1022 gives inf / NaN multipliers, which the growth test below rejects)
+                // sits in the same basic block and is scheduled under the batch's loads and FMAs
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double p4 = prow[k + 4], p5 = prow[k + 5], p6 = prow[k + 6], p7 = prow[k + 7];
+                const double r0 = mine_[k], q1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                const double r4 = mine_[k + 4], r5 = mine_[k + 5], r6 = mine_[k + 6], r7 = mine_[k + 7];
+                double y;
+                asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(den));
+                double e = fma(-den, y, 1.0);
+                e = fma(e, e, e); y = fma(y, e, y);
+                e = fma(-den, y, 1.0); rc = fma(y, e, y);
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, q1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
+                mine_[k + 4] = fma(-l, p4, r4); mine_[k + 5] = fma(-l, p5, r5);
+                mine_[k + 6] = fma(-l, p6, r6); mine_[k + 7] = fma(-l, p7, r7);
+                k += 8;
+            } else rc = 1.0 / den;
+#pragma unroll 1
+            for (; k + 7 <= Ns; k += 8) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double p4 = prow[k + 4], p5 = prow[k + 5], p6 = prow[k + 6], p7 = prow[k + 7];
+                const double r0 = mine_[k], q1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                const double r4 = mine_[k + 4], r5 = mine_[k + 5], r6 = mine_[k + 6], r7 = mine_[k + 7];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, q1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
+                mine_[k + 4] = fma(-l, p4, r4); mine_[k + 5] = fma(-l, p5, r5);
+                mine_[k + 6] = fma(-l, p6, r6); mine_[k + 7] = fma(-l, p7, r7);
+            }
+            if (k <= Ns) {
+                // up to seven elements left: one predicated batch, every load ahead of the first FMA
+                const int r = Ns - k + 1;
+                double pp[7], qq[7];
+#pragma unroll
+                for (int i = 0; i < 7; ++i) if (i < r) { pp[i] = prow[k + i]; qq[i] = mine_[k + i]; }
+#pragma unroll
+                for (int i = 0; i < 7; ++i) if (i < r) mine_[k + i] = fma(-l, pp[i], qq[i]);
+            }
+            mine_[j + 1] = nxt ? rc : r1;
+        }
+    }
+    // accepted when no multiplier grew (NaN fails the comparison as well); barrier inside
+    if (g.any(cx->O.pivoting == 2 || !(gmax <= 1024.0), 2)) return false;
+    if (t == 0) { reinterpret_cast<int*>(WS(CNT))[CNT_LU]++; reinterpret_cast<int*>(WS(CNT))[CNT_DIAG] = 1; }
+    g.sync();
+    return true;
+}
+
+// Build the matrix from the sparse Jacobian and factorise it: LUDecompose (A.10) with implicit row scaling and
+// partial pivoting. Rows never move: `pos` is the index the row would have in the reference's physically swapped
+// matrix (drives its tie rule: the LAST maximal row wins), STEP[t] the column at which row t became the pivot row.
+// With lbchem_options.pivoting != 0 the diagonal-pivot factorisation above is tried first.
+template <bool DAC>
+static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double dg) {
+    if (cx->O.pivoting && lu_factor_diag<DAC>(cx, base, dg)) return 0;
+    const Grp g(base);
+    const int nSp = cx->S.nSp, t = g.tid, N = cx->nEqn;
+    const Compact<DAC> cp(cx, base);
+    const int Ns = cp.Ns, ldc = cp.ldc;
+    const bool mine = t < nSp && cp.kept(t);
+    const int cm = mine ? cp.index(t) : 0;
+    double* A = WS(A);
+    int* STEP = reinterpret_cast<int*>(WS(STEP));
+    int* SPOF = STEP + N + (N & 1);               // DAC: species of compact column j
+    double* XCH = WS(XCH);
+    double* row = A + cm * ldc;
+    g.sync();
+    const double big = lu_build<DAC, true>(cx, base, cp, row, SPOF, mine, cm, dg);
     if (g.any(t < N && big == 0.0, 2)) return LBCHEM_CELL_SINGULAR;
     const double vv = 1.0 / big;
     bool done = !mine;
@@ -654,12 +755,19 @@ static __device__ __noinline__ int lu_factor(const Ctx* cx, double* base, double
             for (; k <= Ns; ++k) mine_[k] = fma(-l, prow[k], mine_[k]);
         }
     }
-    if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_LU]++;
+    if (t == 0) { reinterpret_cast<int*>(WS(CNT))[CNT_LU]++; reinterpret_cast<int*>(WS(CNT))[CNT_DIAG] = 0; }
     g.sync();
     return 0;
 }
 
 // x <- A^-1 x with the factors left by lu_factor (x: shared vector of nEqn, natural order in and out)
+//
+// Factors from the diagonal-pivot path (CNT_DIAG): row order = column order, so the substitutions stay inside a warp.
+// The warp that owns the rows of columns [0, c0) runs them as shuffle steps (the owner lane broadcasts its finished
+// value, no shared memory, no barrier), publishes its part once, and the other warp first folds those c0 columns into
+// its rows as a run of FMAs and then does its own columns the same way; the backward pass mirrors it. Three group
+// barriers per solve instead of one per column; the order of the operations on every row is that of the column loop
+// below (ascending columns forward; temperature column, then descending columns backward).
 template <bool DAC>
 static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double* x) {
     const Grp g(base);
@@ -667,7 +775,8 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
     const Compact<DAC> cp(cx, base);
     const int Ns = cp.Ns;
     const bool sp = t < nSp && cp.kept(t);
-    const double* row = WS(A) + (sp ? cp.index(t) : 0) * cp.ldc;
+    const int cm = sp ? cp.index(t) : 0;
+    const double* row = WS(A) + cm * cp.ldc;
     double* BS = WS(BS);
     const int* SPOF = reinterpret_cast<const int*>(WS(STEP)) + N + (N & 1);
     g.sync();
@@ -675,6 +784,93 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
     const double rdg = WS(XS)[1];                   // 1 / dg: the diagonal rows (T, p, removed species)
     double bt = t < N ? x[t] : 0.0;
     if (t < nSp && !sp) x[t] = bt * rdg;            // removed species: decoupled diagonal row
+    if (reinterpret_cast<const int*>(WS(CNT))[CNT_DIAG]) {
+        constexpr int kW = TPC < 32 ? TPC : 32;                   // lanes of a group inside one warp
+        constexpr bool two = Grp::kTwoWarps;
+        const int lbase = g.lane & ~(kW - 1);
+        // columns [0, c0) belong to the rows of the group's first warp, [c0, Ns) to the second
+        const int c0 = two ? (nSp > 32 ? cp.index(32) : Ns) : Ns;
+        if (t == nSp + 1) x[t] = bt * rdg;
+        if (t == nSp) { const double v = bt * rdg; BS[Ns] = v; x[t] = v; }
+        const int cf = sp ? cm : -1;                              // forward: rows below column j take part (cm > j)
+        const int cb = sp ? cm : 0x7fffffff;                      // backward: rows above column j (cm < j)
+#define LANE_OF(j) (lbase + ((DAC ? SPOF[j] : (j)) & (kW - 1)))
+        // One substitution step = broadcast of the owner's value + one FMA; the matrix element and (DAC) the owner lane of
+        // the NEXT step are fetched before the shuffle, so that only shuffle + FMA sit on the dependent chain.
+#define FWD_STEPS(j0, j1)                                                                                   \
+        {                                                                                                   \
+            double a = row[j0]; int src = LANE_OF(j0);                                                      \
+            _Pragma("unroll 2")                                                                             \
+            for (int j = (j0); j < (j1); ++j) {                                                             \
+                const double an = row[j + 1]; const int nsrc = LANE_OF(j + 1);                              \
+                const double xj = __shfl_sync(g.mask, bt, src);                                             \
+                if (cf > j) bt = fma(-a, xj, bt);                                                           \
+                a = an; src = nsrc;                                                                         \
+            }                                                                                               \
+        }
+        // folds the columns [j0, j1) another warp has finished (values in BS) into this row: four partial sums
+#define FOLD(j0, j1)                                                                                        \
+        {                                                                                                   \
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0; int j = (j0);                                    \
+            _Pragma("unroll 1")                                                                             \
+            for (; j + 3 < (j1); j += 4) {                                                                  \
+                const double a0 = row[j], a1 = row[j + 1], a2 = row[j + 2], a3 = row[j + 3];                \
+                const double b0 = BS[j], b1 = BS[j + 1], b2 = BS[j + 2], b3 = BS[j + 3];                    \
+                s0 = fma(a0, b0, s0); s1 = fma(a1, b1, s1); s2 = fma(a2, b2, s2); s3 = fma(a3, b3, s3);     \
+            }                                                                                               \
+            _Pragma("unroll 1")                                                                             \
+            for (; j < (j1); ++j) s0 = fma(row[j], BS[j], s0);                                              \
+            bt -= (s0 + s1) + (s2 + s3);                                                                    \
+        }
+        // forward substitution, unit lower triangle
+        if (!two || g.warp == 0) {
+            FWD_STEPS(0, c0)
+            if (two && sp) BS[cm] = bt;
+        }
+        g.sync();
+        if (two && g.warp == 1) {
+            if (sp) FOLD(0, c0)
+            FWD_STEPS(c0, Ns)
+        }
+        // backward substitution on the row scaled by its reciprocal pivot: s = (b - sum U x) / pivot is kept up to date as
+        // s -= (U[., j] / pivot) x_j, so the owner of column j holds x_j the moment the columns above it are done and the
+        // step is again shuffle + FMA. The temperature column goes first (BS[Ns] was published before the barrier above).
+        const double rd = sp ? row[cm] : 0.0;
+        if (sp) bt = fma(-row[Ns], BS[Ns], bt);
+        double s = bt * rd;
+#define BWD_STEPS(j1, j0)                                                                                   \
+        {                                                                                                   \
+            double ur = row[(j1) - 1] * rd; int src = LANE_OF((j1) - 1);                                    \
+            _Pragma("unroll 2")                                                                             \
+            for (int j = (j1) - 1; j >= (j0); --j) {                                                        \
+                const int jn = j > 0 ? j - 1 : 0;                                                           \
+                const double urn = row[jn] * rd; const int nsrc = LANE_OF(jn);                              \
+                const double xj = __shfl_sync(g.mask, s, src);                                              \
+                if (cb < j) s = fma(-ur, xj, s);                                                            \
+                ur = urn; src = nsrc;                                                                       \
+            }                                                                                               \
+        }
+        if (!two) { BWD_STEPS(Ns, 0) }
+        else {
+            if (g.warp == 1) {
+                BWD_STEPS(Ns, c0)
+                if (sp) BS[cm] = s;
+            }
+            g.sync();
+            if (g.warp == 0) {
+                if (sp) { FOLD(c0, Ns) s = bt * rd; }
+                BWD_STEPS(c0, 0)
+            }
+        }
+#undef LANE_OF
+#undef FWD_STEPS
+#undef BWD_STEPS
+#undef FOLD
+        if (sp) x[t] = s;
+        if (t == 0) reinterpret_cast<int*>(WS(CNT))[CNT_SOLVE]++;
+        g.sync();
+        return;
+    }
     // forward substitution, unit lower triangle (the T and p rows have no sub-diagonal entries)
 #pragma unroll 1
     for (int j = 0; j < Ns; ++j) {

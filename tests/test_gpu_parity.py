@@ -135,6 +135,46 @@ def test_gri_flame_fixture_parity(gri, flame, solver, rel_tol, kernel, monkeypat
     chem.close()
 
 
+@pytest.mark.parametrize("solver,rel_tol", [("Rosenbrock34", 1e-2), ("seulex", 1e-1)])
+def test_pivoting_rules(gri, flame, solver, rel_tol):
+    """lbchem_options.pivoting. The parity tests above run the default (1: diagonal pivots, growth test, the reference's
+    rule as fallback). Here: (a) rule 0 -- LUDecompose's own pivot sequence on every matrix -- against the oracle on all
+    4000 cells at the same 1e-6; (b) the fallback of rule 1 (hook 2 rejects every diagonal factorisation) reproduces
+    rule 0 bit for bit; (c) rule 1 stays within 1e-6 of rule 0 in every output field, DAC-reduced systems included."""
+    sel = np.arange(flame["T"].shape[0])
+    Y, T, p, rho = _state(gri, flame, sel)
+    out = {}
+    for piv in (0, 1, 2):
+        opts = capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, pivoting=piv)
+        chem = capi.Chemistry(gri, opts)
+        out[piv] = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+        out[piv, "lu"] = chem.stats()["n_lu"]
+        chem.close()
+    ref = O.OracleModel(gri, capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol)).solve_batch(Y, T, p, rho, DT, DTCHEM, nthreads=8)
+    _compare(gri, Y, rho, out[0], ref, DT, f"gri/{solver}/pivoting=0")
+    for k in ("RR", "T", "deltaTChem", "cost", "status"):
+        assert np.array_equal(out[0][k], out[2][k]), f"fallback differs from rule 0 in {k}"
+    assert out[0, "lu"] == out[2, "lu"]                       # a rejected diagonal attempt is not an algorithmic LU
+    a, b = out[0], out[1]
+    W = gri.W[:, None]
+    eR = (np.abs(a["RR"] - b["RR"]) / (np.abs(a["RR"]) + 1e-12 * W / DT)).max()
+    eT = (np.abs(a["T"] - b["T"]) / a["T"]).max()
+    print(f"{solver}: pivoting 1 vs 0: RR {eR:.2e} T {eT:.2e}, cells with another attempt count {int((a['cost'] != b['cost']).sum())}")
+    assert eR < RTOL and eT < RTOL and (a["status"] == b["status"]).all()
+    assert (a["cost"] != b["cost"]).mean() <= 0.01
+    # DAC-reduced systems (compacted rows and columns): rule 1 against rule 0
+    init = [list(gri.species).index(s) for s in ("CO", "CH4", "HO2")]
+    dac = {}
+    for piv in (0, 1):
+        chem = capi.Chemistry(gri, capi.default_options(solver=solver, abs_tol=1e-12, rel_tol=rel_tol, pivoting=piv))
+        chem.set_reduction(1e-4, init)
+        dac[piv] = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+        chem.close()
+    eR = (np.abs(dac[0]["RR"] - dac[1]["RR"]) / (np.abs(dac[0]["RR"]) + 1e-12 * W / DT)).max()
+    print(f"{solver}: DAC, pivoting 1 vs 0: RR {eR:.2e}")
+    assert eR < RTOL and (dac[0]["status"] == dac[1]["status"]).all()
+
+
 # ---- the other BASELINE configurations (parity-test cases, not bench lines) -------------------------
 def _solve_both(mech, Y, T, p, rho, opts, dt=DT, dtchem=DTCHEM):
     chem = capi.Chemistry(mech, opts)
