@@ -1,6 +1,6 @@
 #!/bin/bash
 mkdir -p gpurun_out
-./scripts/lat_bench > gpurun_out/lat_bench.txt 2>&1; cat gpurun_out/lat_bench.txt
+
 timeout 900 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -s -k "pivoting or fixture_parity or h2_air or ch4_one or dac_parity or probes" > gpurun_out/piv_pytest.log 2>&1
 echo "pytest exit $?" >> gpurun_out/piv_pytest.log
 tail -3 gpurun_out/piv_pytest.log
@@ -19,4 +19,5 @@ run s_p1 --workload gri_uniform --solver seulex --cells 200000 --pivoting 1
 run r_p1 --workload gri_uniform --solver Rosenbrock34 --cells 200000 --pivoting 1
 run h2_p1 --workload h2_air --solver Rosenbrock34 --cells 1000000 --pivoting 1
 run ch4_p1 --workload ch4_mixing --solver Rosenbrock34 --cells 1000000 --pivoting 1
-run dac_p1 --workload gri_dac --solver seulex --cells 400000 --pivoting 1
+LBCHEM_VERBOSE=1 run dac_p1 --workload gri_dac --solver seulex --cells 400000 --pivoting 1; grep "v3 kernel:" gpurun_out/piv_dac_p1.err | tail -1
+run s_p0 --workload gri_uniform --solver seulex --cells 200000 --pivoting 0
