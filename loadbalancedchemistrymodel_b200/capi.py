@@ -6,6 +6,7 @@ shared object is missing or a CUDA device is absent, calls fail loudly.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -13,7 +14,8 @@ import numpy as np
 from .foam_io import Mechanism
 
 _HERE = Path(__file__).resolve().parent
-LIB_PATH = _HERE / "csrc" / "liblbchem.so"
+# LBCHEM_LIB: another build of the same library (A/B runs of kernel variants, scripts/gpu_var.sh); never a different implementation
+LIB_PATH = Path(os.environ["LBCHEM_LIB"]) if os.environ.get("LBCHEM_LIB") else _HERE / "csrc" / "liblbchem.so"
 
 SOLVER_NONE, SOLVER_EULER_IMPLICIT, SOLVER_ROSENBROCK34, SOLVER_SEULEX = 0, 1, 2, 3
 SOLVERS = {

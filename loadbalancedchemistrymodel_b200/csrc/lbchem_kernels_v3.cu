@@ -27,7 +27,7 @@ struct SMech {            // typed views into the staged blob
     const double *W, *Tc, *cpLo, *cpHi, *haLo, *haHi, *sLo, *sHi;
     const double *A, *beta, *Ta, *fall, *tcTab, *effVal;
     const unsigned* info; const unsigned long long *lpk, *rpk;
-    const int *effPtr, *effSp, *spPtr, *rowPtr;
+    const int *effPtr, *effSp, *spPtr, *rowPtr, *gaTab;
     const unsigned short* spList; const unsigned char* entCol;
 };
 
@@ -39,7 +39,7 @@ __device__ __forceinline__ void bind(SMech& S, const V2Mech& M, const unsigned c
     S.A = P(double, oA); S.beta = P(double, oBeta); S.Ta = P(double, oTa); S.fall = P(double, oFall);
     S.tcTab = P(double, oTcTab); S.effVal = P(double, oEffVal);
     S.info = P(unsigned, oInfo); S.lpk = P(unsigned long long, oLpk); S.rpk = P(unsigned long long, oRpk);
-    S.effPtr = P(int, oEffPtr); S.effSp = P(int, oEffSp); S.spPtr = P(int, oSpPtr); S.rowPtr = P(int, oRowPtr);
+    S.effPtr = P(int, oEffPtr); S.effSp = P(int, oEffSp); S.spPtr = P(int, oSpPtr); S.rowPtr = P(int, oRowPtr); S.gaTab = P(int, oGaTab);
     S.spList = P(unsigned short, oSpList); S.entCol = P(unsigned char, oEntCol);
 #undef P
 }
@@ -358,16 +358,20 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
     g.sync();
 }
 
-// dc_i/dt = sum over the reactions of species i of nu * omega. Four interleaved partial sums (terms k, k+1, k+2, k+3
-// of the reference's order), combined as (a0 + a1) + (a2 + a3): the species with > 100 reactions (H, OH, O ...)
-// would otherwise serialise one ~30-cycle dependent FMA per term while the rest of the group waits at the barrier.
-static __device__ __forceinline__ double gather_species(const SMech& S, const double* om, int i) {
+// dc_i/dt = sum over the reactions of species i of nu * omega: four interleaved partial sums (terms k, k+1, k+2, k+3 of the
+// reference's order, combined as (a0 + a1) + (a2 + a3)) over 16-bit list entries read four at a time (lists padded with nu = 0).
+// The species sums of a whole group, dealt to all its threads (host: gaTab): thread t walks its part of a list, the threads
+// past the species rows hand their partial sums to the owners through the exchange scratch, one group barrier. Returns
+// dc_t/dt in thread t < nSp (own part + helper parts in list order), 0 elsewhere. Call with every thread of the group.
+static __device__ __forceinline__ double gather_all(const Grp& g, const Ctx* cx, double* base) {
+    const SMech& S = cx->S;
+    const double* om = WS(OM);
+    const int t = g.tid, nSp = S.nSp;
     double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
-    const int e = S.spPtr[i + 1];
-    // lists are padded to multiples of four 16-bit entries (nu = 0 padding adds an exact zero): one 64-bit load per four terms
+    const int e = S.gaTab[64 + t];
     const unsigned long long* L = reinterpret_cast<const unsigned long long*>(S.spList);
 #pragma unroll 1
-    for (int k = S.spPtr[i]; k < e; k += 4) {
+    for (int k = S.gaTab[t]; k < e; k += 4) {
         const unsigned long long w = L[k >> 2];
         const int u0 = (int)(short)(w & 0xffffu), u1 = (int)(short)((w >> 16) & 0xffffu), u2 = (int)(short)((w >> 32) & 0xffffu),
                   u3 = (int)(short)(w >> 48);
@@ -376,7 +380,17 @@ static __device__ __forceinline__ double gather_species(const SMech& S, const do
         a2 = fma((double)(u2 >> 12), om[u2 & 0xfff], a2);
         a3 = fma((double)(u3 >> 12), om[u3 & 0xfff], a3);
     }
-    return (a0 + a1) + (a2 + a3);
+    double v = (a0 + a1) + (a2 + a3);
+    if (S.gaTab[191] == 0) return t < nSp ? v : 0.0;          // short lists (small mechanisms): nothing was split
+    double* H = g.red + 16;                       // slots 2 and 3 of the exchange scratch
+    if (t >= nSp && t < nSp + 16) H[t - nSp] = v;
+    g.sync();
+    if (t < nSp) {
+        const int h = S.gaTab[128 + t];
+#pragma unroll 1
+        for (int i = 0; i < (h >> 8); ++i) v += H[(h & 255) + i];
+    } else v = 0.0;
+    return v;
 }
 
 // tail of StandardChemistryModel::derivatives: dT/dt = -sum h_i w_i / (rho cp) from the species rates `d` (thread t owns
@@ -412,7 +426,7 @@ static __device__ __noinline__ void derivatives(const Ctx* cx, double* base, con
     const double lnT = log(T), invT = 1.0 / T;
     prepare(g, cx, base, y, T, lnT, true);
     reaction_sweep<DAC>(cx, base, 0, T, lnT, invT);
-    finish_derivatives(g, cx, base, T, t < nSp ? gather_species(S, WS(OM), t) : 0.0, dydt);
+    finish_derivatives(g, cx, base, T, gather_all(g, cx, base), dydt);
 }
 
 // StandardChemistryModel::jacobian (A.9) into the sparse store: JS[entry] (species block, structural
@@ -435,7 +449,7 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
         if (pass == 0) {
             // species rates at (y, T): the dfdx slot (A.4 quirk) and, on request, the full derivatives() at the same state
             // (adaptiveSolver's dydx0: the reference evaluates it separately from the same rates)
-            const double d0 = (t < nSp && ((dfdx && cx->O.dfdxIsDcdt) || dydt0)) ? gather_species(S, WS(OM), t) : 0.0;
+            const double d0 = ((dfdx && cx->O.dfdxIsDcdt) || dydt0) ? gather_all(g, cx, base) : 0.0;
             if (dfdx && t < N) dfdx[t] = (t < nSp && cx->O.dfdxIsDcdt) ? d0 : 0.0;
             if (dydt0) finish_derivatives(g, cx, base, T, d0, dydt0);
             // (1) D terms: k * product of the other concentrations, one per (reaction, side, species), into the matrix
@@ -486,9 +500,9 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
 #pragma unroll
                 for (int q = 0; q < PF; ++q) cur[q] = nxt[q];
             }
-        } else if (t < nSp) {
-            const double d = gather_species(S, WS(OM), t);
-            if (pass == 1) dp = d; else GS_JT[t] = 0.5 * (dp - d) / delta;
+        } else {
+            const double d = gather_all(g, cx, base);
+            if (t < nSp) { if (pass == 1) dp = d; else GS_JT[t] = 0.5 * (dp - d) / delta; }
         }
         g.sync();
     }

@@ -35,7 +35,7 @@ struct V2Mech {
     int oW, oTc, oCpLo, oCpHi, oHaLo, oHaHi, oSLo, oSHi;
     int oA, oBeta, oTa, oInfo, oLpk, oRpk, oFall, oTcTab;
     int oEffPtr, oEffSp, oEffVal;
-    int oSpPtr, oSpList;
+    int oSpPtr, oSpList, oGaTab;
     int oRowPtr, oEntCol;
     const unsigned char* blob;           // global copy of the blob
     // Jacobian: D-term program [nD] (k index and the three concentration factors of d omega / d c), then the entry gather

@@ -250,6 +250,36 @@ int lb_v2_build(const lbchem_mech_desc* m, V2Mech* out, std::vector<void*>& allo
         }
         if (spList.empty()) spList.assign(4, 0);
         M.oSpPtr = B.add(spPtr); M.oSpList = B.add(spList);
+        // Balanced gather: the species sums are dealt to ALL threads of a group. The threads past the species rows
+        // (T, p, padding lanes: 11 of 64 for GRI) take parts of the longest lists -- H has 148 terms against a mean of
+        // 25 -- so that no lane walks more than ~40. gaTab: [0, 64) first entry, [64, 128) end entry of thread t;
+        // [128, 192) owners: first helper slot | helper count << 8 (helper thread nSp + s writes slot s, at most 16 slots); [191] slots in use
+        {
+            const int tpc = N <= 8 ? 8 : (N <= 16 ? 16 : (N <= 32 ? 32 : 64));
+            const int nHelp = std::min(16, std::max(0, tpc - nSp));
+            std::vector<int> parts(nSp, 1);
+            auto quads = [&](int i) { return (spPtr[i + 1] - spPtr[i]) / 4; };
+            auto worst = [&](int i) { return (quads(i) + parts[i] - 1) / parts[i]; };
+            for (int h = 0; h < nHelp; ++h) {
+                int best = 0;
+                for (int i = 1; i < nSp; ++i) if (worst(i) > worst(best)) best = i;
+                if (worst(best) <= 6) break;                       // lists of <= 24 terms stay whole (H2/O2, 1-step CH4: no helpers, no barrier)
+                parts[best]++;
+            }
+            std::vector<int> ga(3 * 64, 0);
+            int slot = 0;
+            for (int i = 0; i < nSp; ++i) {
+                const int q = quads(i), n = parts[i], per = (q + n - 1) / n;
+                ga[i] = spPtr[i]; ga[64 + i] = spPtr[i] + 4 * std::min(q, per);
+                ga[128 + i] = slot | ((n - 1) << 8);
+                for (int k = 1; k < n; ++k, ++slot) {
+                    const int t = nSp + slot;
+                    ga[t] = spPtr[i] + 4 * std::min(q, k * per); ga[64 + t] = spPtr[i] + 4 * std::min(q, (k + 1) * per);
+                }
+            }
+            ga[191] = slot;                                        // helper slots in use (thread 63 never owns a species: nSp <= 62)
+            M.oGaTab = B.add(ga);
+        }
     }
 
     // Jacobian: (1) "D terms" d(omega_r)/d(c_col) / nu = k * prod of the other concentrations, one per (reaction, side,
