@@ -651,15 +651,15 @@ static __device__ __noinline__ bool lu_factor_diag(const Ctx* cx, double* base, 
                 mine_[k + 4] = fma(-l, p4, r4); mine_[k + 5] = fma(-l, p5, r5);
                 mine_[k + 6] = fma(-l, p6, r6); mine_[k + 7] = fma(-l, p7, r7);
             }
-            if (k <= Ns) {
-                // up to seven elements left: one predicated batch, every load ahead of the first FMA
-                const int r = Ns - k + 1;
-                double pp[7], qq[7];
-#pragma unroll
-                for (int i = 0; i < 7; ++i) if (i < r) { pp[i] = prow[k + i]; qq[i] = mine_[k + i]; }
-#pragma unroll
-                for (int i = 0; i < 7; ++i) if (i < r) mine_[k + i] = fma(-l, pp[i], qq[i]);
+#pragma unroll 1
+            for (; k + 3 <= Ns; k += 4) {
+                const double p0 = prow[k], p1 = prow[k + 1], p2 = prow[k + 2], p3 = prow[k + 3];
+                const double r0 = mine_[k], q1 = mine_[k + 1], r2 = mine_[k + 2], r3 = mine_[k + 3];
+                mine_[k] = fma(-l, p0, r0); mine_[k + 1] = fma(-l, p1, q1);
+                mine_[k + 2] = fma(-l, p2, r2); mine_[k + 3] = fma(-l, p3, r3);
             }
+#pragma unroll 1
+            for (; k <= Ns; ++k) mine_[k] = fma(-l, prow[k], mine_[k]);
             mine_[j + 1] = nxt ? rc : r1;
         }
     }
@@ -814,7 +814,7 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
 #define FWD_STEPS(j0, j1)                                                                                   \
         {                                                                                                   \
             double a = row[j0]; int src = LANE_OF(j0);                                                      \
-            _Pragma("unroll 2")                                                                             \
+            _Pragma("unroll 1")                                                                             \
             for (int j = (j0); j < (j1); ++j) {                                                             \
                 const double an = row[j + 1]; const int nsrc = LANE_OF(j + 1);                              \
                 const double xj = __shfl_sync(g.mask, bt, src);                                             \
@@ -855,7 +855,7 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
 #define BWD_STEPS(j1, j0)                                                                                   \
         {                                                                                                   \
             double ur = row[(j1) - 1] * rd; int src = LANE_OF((j1) - 1);                                    \
-            _Pragma("unroll 2")                                                                             \
+            _Pragma("unroll 1")                                                                             \
             for (int j = (j1) - 1; j >= (j0); --j) {                                                        \
                 const int jn = j > 0 ? j - 1 : 0;                                                           \
                 const double urn = row[jn] * rd; const int nsrc = LANE_OF(jn);                              \
