@@ -477,7 +477,7 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
             // (2) entry gather program: acc += coef * D[term], entry closed by the `last` flag. The program streams from
             //     global memory (L2): eight words are fetched ahead so that one round trip is paid per eight terms
             const int nT = cx->jthrN[t];
-            int e = cx->jthrEnt[t];
+            double* jsp = JS + cx->jthrEnt[t];
             double acc = 0.0;
             const unsigned* prog = cx->jterm + t;
             constexpr int PF = 8;
@@ -491,11 +491,10 @@ static __device__ __noinline__ void jacobian(const Ctx* cx, double* base, const 
                 for (int q = 0; q < PF; ++q) nxt[q] = prog[(size_t)(k0 + PF + q) * TPC];
 #pragma unroll
                 for (int q = 0; q < PF; ++q) {
-                    if (k0 + q < nT) {
-                        const unsigned wd = cur[q];
-                        acc = fma((double)V2_J_COEF(wd), D[V2_J_D(wd)], acc);
-                        if (V2_J_LAST(wd)) { JS[e++] = acc; acc = 0.0; }
-                    }
+                    // words past a thread's last term are zero (host padding): they add 0 * D[0] to a sum that is never stored
+                    const unsigned wd = cur[q];
+                    acc = fma((double)V2_J_COEF(wd), D[V2_J_D(wd)], acc);
+                    if (V2_J_LAST(wd)) { *jsp++ = acc; acc = 0.0; }
                 }
 #pragma unroll
                 for (int q = 0; q < PF; ++q) cur[q] = nxt[q];
@@ -809,17 +808,14 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
         const int cf = sp ? cm : -1;                              // forward: rows below column j take part (cm > j)
         const int cb = sp ? cm : 0x7fffffff;                      // backward: rows above column j (cm < j)
 #define LANE_OF(j) (lbase + ((DAC ? SPOF[j] : (j)) & (kW - 1)))
-        // One substitution step = broadcast of the owner's value + one FMA; the matrix element and (DAC) the owner lane of
-        // the NEXT step are fetched before the shuffle, so that only shuffle + FMA sit on the dependent chain.
+        // One substitution step = broadcast of the owner's value + one FMA (look-ahead loads and a pre-scaled backward chain
+        // were measured: no gain, more instructions).
 #define FWD_STEPS(j0, j1)                                                                                   \
         {                                                                                                   \
-            double a = row[j0]; int src = LANE_OF(j0);                                                      \
             _Pragma("unroll 1")                                                                             \
             for (int j = (j0); j < (j1); ++j) {                                                             \
-                const double an = row[j + 1]; const int nsrc = LANE_OF(j + 1);                              \
-                const double xj = __shfl_sync(g.mask, bt, src);                                             \
-                if (cf > j) bt = fma(-a, xj, bt);                                                           \
-                a = an; src = nsrc;                                                                         \
+                const double xj = __shfl_sync(g.mask, bt, LANE_OF(j));                                      \
+                if (cf > j) bt = fma(-row[j], xj, bt);                                                      \
             }                                                                                               \
         }
         // folds the columns [j0, j1) another warp has finished (values in BS) into this row: four partial sums
@@ -846,22 +842,17 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
             if (sp) FOLD(0, c0)
             FWD_STEPS(c0, Ns)
         }
-        // backward substitution on the row scaled by its reciprocal pivot: s = (b - sum U x) / pivot is kept up to date as
-        // s -= (U[., j] / pivot) x_j, so the owner of column j holds x_j the moment the columns above it are done and the
-        // step is again shuffle + FMA. The temperature column goes first (BS[Ns] was published before the barrier above).
-        const double rd = sp ? row[cm] : 0.0;
+        // backward substitution: the temperature column first (BS[Ns] was published before the barrier above), then the
+        // species columns in descending order; the owner of column j broadcasts x_j = b_j / pivot_j
         if (sp) bt = fma(-row[Ns], BS[Ns], bt);
-        double s = bt * rd;
+        double s = 0.0;
 #define BWD_STEPS(j1, j0)                                                                                   \
         {                                                                                                   \
-            double ur = row[(j1) - 1] * rd; int src = LANE_OF((j1) - 1);                                    \
             _Pragma("unroll 1")                                                                             \
             for (int j = (j1) - 1; j >= (j0); --j) {                                                        \
-                const int jn = j > 0 ? j - 1 : 0;                                                           \
-                const double urn = row[jn] * rd; const int nsrc = LANE_OF(jn);                              \
-                const double xj = __shfl_sync(g.mask, s, src);                                              \
-                if (cb < j) s = fma(-ur, xj, s);                                                            \
-                ur = urn; src = nsrc;                                                                       \
+                const double xj = __shfl_sync(g.mask, bt * row[j], LANE_OF(j));                             \
+                if (cb < j) bt = fma(-row[j], xj, bt);                                                      \
+                if (cb == j) s = xj;                                                                        \
             }                                                                                               \
         }
         if (!two) { BWD_STEPS(Ns, 0) }
@@ -872,7 +863,7 @@ static __device__ __noinline__ void lu_solve(const Ctx* cx, double* base, double
             }
             g.sync();
             if (g.warp == 0) {
-                if (sp) { FOLD(c0, Ns) s = bt * rd; }
+                if (sp) { FOLD(c0, Ns) }
                 BWD_STEPS(c0, 0)
             }
         }
