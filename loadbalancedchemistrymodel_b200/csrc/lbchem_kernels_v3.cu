@@ -111,8 +111,10 @@ __device__ __forceinline__ double js(const double* q, int st, double T, double l
     return (((q[0] * T + q[1 * st]) * T + q[2 * st]) * T + q[3 * st]) * T + q[4 * st] * lnT + q[5 * st];
 }
 
-__device__ __forceinline__ double cpow(double c, unsigned e) {   // e in 1..3
-    return e == 1 ? c : (e == 2 ? c * c : c * c * c);
+__device__ __forceinline__ double cpow(double c, unsigned e) {   // e in 1..3; 1 in nearly every slot: two untaken branches
+    double r = c;
+    if (e > 1) { r = c * c; if (e > 2) r = r * c; }
+    return r;
 }
 
 __device__ __forceinline__ double side_product(const double* c, unsigned long long pk, unsigned n) {
@@ -309,7 +311,7 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
                 const double nn = 0.75 - 1.27 * logFcent;
                 const double logPr = log10(fmax(Pr, LB_SMALL));
                 const double q2 = (logPr + cc) / (nn - 0.14 * (logPr + cc));
-                F = pow(10.0, logFcent / (1.0 + q2 * q2));
+                F = exp(2.302585092994046 * (logFcent / (1.0 + q2 * q2)));      // 10^y
             }
             OM[p] = kInf * (Pr / (1 + Pr)) * F;
         }
@@ -329,15 +331,23 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
             k = S.A[p] * k;
             if (ty == LBCHEM_R_THIRD_BODY) k = ME[V2_EFF(iw)] * k;
         }
-        double kr = 0.0;
+        double kr = 0.0, pl = 1.0, pr = 1.0;
+        const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
         if (V2_REV(iw)) {
+            // one walk over the slots of each side gives the Gibbs sum (right side first, as the reference adds them) and
+            // the concentration product
             const double* G = (T < S.tcTab[V2_TCI(iw)]) ? GL : GH;
-            const unsigned long long lp = S.lpk[p], rp = S.rpk[p];
             double gs = 0.0;
 #pragma unroll 1
-            for (unsigned s = 0; s < V2_NR(iw); ++s) { const unsigned sl = V2_SLOT(rp, s); gs = fma((double)V2_NU(sl), G[V2_SP(sl)], gs); }
+            for (unsigned s = 0; s < V2_NR(iw); ++s) {
+                const unsigned sl = V2_SLOT(rp, s), sp = V2_SP(sl);
+                gs = fma((double)V2_NU(sl), G[sp], gs); pr *= cpow(CC[sp], V2_EX(sl));
+            }
 #pragma unroll 1
-            for (unsigned s = 0; s < V2_NL(iw); ++s) { const unsigned sl = V2_SLOT(lp, s); gs = fma(-(double)V2_NU(sl), G[V2_SP(sl)], gs); }
+            for (unsigned s = 0; s < V2_NL(iw); ++s) {
+                const unsigned sl = V2_SLOT(lp, s), sp = V2_SP(sl);
+                gs = fma(-(double)V2_NU(sl), G[sp], gs); pl *= cpow(CC[sp], V2_EX(sl));
+            }
             const double arg = -gs * invT;
             double Kc = (arg < 600.0) ? exp(arg) : LB_VGREAT;
             const int dn = (int)V2_DNC(iw) - 3;
@@ -347,9 +357,9 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
                 else Kc *= pow(x, (double)dn);
             }
             kr = k / fmax(Kc, kcFloor);
-        }
-        const double f = k * side_product(CC, S.lpk[p], V2_NL(iw));
-        const double b = kr * side_product(CC, S.rpk[p], V2_NR(iw));
+        } else pl = side_product(CC, lp, V2_NL(iw));
+        const double f = k * pl;
+        const double b = kr * pr;
         OM[p] = f - b;
         if (keep) { KF[p] = k; KR[p] = kr; }
     }
@@ -605,7 +615,7 @@ static __device__ __noinline__ bool lu_factor_diag(const Ctx* cx, double* base, 
     if (mine && cm == 0) { const double d = row[0]; row[0] = 1.0 / ((d == 0.0) ? LB_SMALL : d); }
     if (t < N) STEP[t] = mine ? cm : -1;
     if (t == 0) WS(XS)[1] = 1.0 / dg;
-    double gmax = 0.0;
+    bool grown = false;
 #pragma unroll 1
     for (int j = 0; j < Ns; ++j) {
         g.sync();
@@ -618,7 +628,7 @@ static __device__ __noinline__ bool lu_factor_diag(const Ctx* cx, double* base, 
             const bool nxt = cm == k;
             const double den = nxt ? ((r1 == 0.0) ? LB_SMALL : r1) : 1.0;
             double rc;
-            mine_[j] = l; gmax = fmax(gmax, fabs(l));
+            mine_[j] = l; grown |= !(fabs(l) <= 1024.0);
             ++k;
             if (k + 7 <= Ns) {
                 // first batch of the row, peeled: the Newton chain of the reciprocal (the one 1.0 / den compiles to, without
@@ -663,7 +673,7 @@ static __device__ __noinline__ bool lu_factor_diag(const Ctx* cx, double* base, 
         }
     }
     // accepted when no multiplier grew (NaN fails the comparison as well); barrier inside
-    if (g.any(cx->O.pivoting == 2 || !(gmax <= 1024.0), 2)) return false;
+    if (g.any(cx->O.pivoting == 2 || grown, 2)) return false;
     if (t == 0) { reinterpret_cast<int*>(WS(CNT))[CNT_LU]++; reinterpret_cast<int*>(WS(CNT))[CNT_DIAG] = 1; }
     g.sync();
     return true;
