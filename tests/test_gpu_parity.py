@@ -23,7 +23,7 @@ def _state(mech, flame, sel):
     return Y, T, p, O.density(mech, Y, T, p)
 
 
-def _compare(mech, Y, rho, got, ref, dt, tag, abs_tol=1e-12, max_other_count=0.01, dtchem_tol=1e-5):
+def _compare(mech, Y, rho, got, ref, dt, tag, abs_tol=1e-12, max_other_count=0.01, dtchem_tol=1e-5, rr_noise_ulps=0):
     """rel 1e-6 on Y, T and RR. The absolute floor is 1e-6 x the integrator's own absTol (a concentration,
     kmol/m3) expressed in each quantity's units: species far below absTol (Y ~ 1e-26 radicals in cold cells)
     are round-off of both implementations, not results."""
@@ -33,7 +33,10 @@ def _compare(mech, Y, rho, got, ref, dt, tag, abs_tol=1e-12, max_other_count=0.0
     Yr = Y + ref["RR"] * dt / rho
     eY = np.abs(Yg - Yr) / (np.abs(Yr) + abs_tol * W / rho)
     eT = np.abs(got["T"] - ref["T"]) / ref["T"]
-    eR = np.abs(got["RR"] - ref["RR"]) / (np.abs(ref["RR"]) + abs_tol * W / np.asarray(dt))
+    # RR = (c - c0) W / deltaT carries the representation noise of c itself: `rr_noise_ulps` ulps of c0 (accumulated over the
+    # sub-steps of a long integration) are not a difference of results, only what goes beyond them is held to 1e-6
+    noise = rr_noise_ulps * np.finfo(float).eps * (rho * Y / W) * W / np.asarray(dt)
+    eR = np.maximum(np.abs(got["RR"] - ref["RR"]) - noise, 0.0) / (np.abs(ref["RR"]) + abs_tol * W / np.asarray(dt))
     same = got["cost"] == ref["attempts"]
     eD = np.abs(got["deltaTChem"] - ref["deltaTChem"])[same] / ref["deltaTChem"][same]
     other = ~same
@@ -494,7 +497,9 @@ def test_seulex_tight_tolerance_uses_the_full_extrapolation_table(gri, flame):
     # many more sub-steps per cell at this tolerance: more last-sub-step coin tosses (see _compare), same states
     # (the proposed next sub-step is err^(-1/(k+1)) of an error estimate that is itself a difference of nearly equal
     # extrapolation columns at this tolerance: its last digits are round-off, hence 1e-4 on deltaTChem here)
-    _compare(gri, Y, rho, got, ref, 1e-5, "seulex 1e-8", abs_tol=1e-14, max_other_count=0.15, dtchem_tol=1e-4)
+    # ~600 sub-steps per cell: N2, which changes by 1e-9 of its concentration over the step, comes back 8 ulps of c apart
+    # from the oracle (1.2e-6 of its RR; Y agrees to 6e-11): 32 ulps of c0 are allowed as representation noise of RR
+    _compare(gri, Y, rho, got, ref, 1e-5, "seulex 1e-8", abs_tol=1e-14, max_other_count=0.15, dtchem_tol=1e-4, rr_noise_ulps=32)
 
 
 def test_host_pipeline_with_pinned_buffers_equals_device_path(gri, flame, monkeypatch):
