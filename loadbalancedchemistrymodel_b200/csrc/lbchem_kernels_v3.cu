@@ -319,6 +319,7 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
     }
     // (3) kf, kr, omega
     const double x = LB_PSTD / (cx->O.RR * T);
+    const double xinv = 1.0 / x;                  // the factor of every reaction that loses a mole: one division per sweep
     const double kcFloor = cx->O.kcFloor;
     double* KF = WS(A); double* KR = KF + nR;
 #pragma unroll 1
@@ -353,7 +354,7 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
             const int dn = (int)V2_DNC(iw) - 3;
             if (dn != 0) {
                 if (dn == 1) Kc *= x;
-                else if (dn == -1) Kc *= 1.0 / x;
+                else if (dn == -1) Kc *= xinv;
                 else Kc *= pow(x, (double)dn);
             }
             kr = k / fmax(Kc, kcFloor);
@@ -550,7 +551,7 @@ static __device__ __forceinline__ double lu_build(const Ctx* cx, double* base, c
     const int t = threadIdx.x % TPC, Ns = cp.Ns;
     double big = fabs(dg);
     if (mine) {
-#pragma unroll 1
+#pragma unroll 4
         for (int k = 0; k <= Ns; ++k) row[k] = 0.0;
         const double* JS = GS_JS;
         const int e1 = S.rowPtr[t + 1];
