@@ -400,6 +400,13 @@ int lbchem_set_reduction(lbchem_handle h, int32_t active, double tolerance, int3
         lb_v3_workspace(probe, LBCHEM_SOLVER_ROSENBROCK34, 1e-2, 1e-12);
         const int cap = std::max(h->V2.nSp * (h->V2.nSp + 1), 2 * h->V2.nR);
         if (h->dacPairs + (h->dacPairs + 7) / 8 > cap) return fail(h, LBCHEM_E_UNSUPPORTED, "reduction: species-pair table does not fit the per-cell workspace");
+        // the enabled-reaction list may live in the tail of the matrix region when nothing else reaches it: the largest
+        // reduced matrix (nSp - 1 species), KF / KR + the Jacobian's D terms, the pair numerators of the reduction pass
+        const int nSp = h->V2.nSp, lda = (nSp + 1) | 1, region = std::max(nSp * lda, 2 * h->V2.nR + h->V2.nD);
+        const int tail = region - (1 + (h->V2.nR + 3) / 4);
+        const int redMat = (nSp - 1) * (nSp | 1);
+        h->V2.rlInMatrix = (redMat <= tail && 2 * h->V2.nR + h->V2.nD <= tail && h->dacPairs + (h->dacPairs + 7) / 8 <= tail) ? 1 : 0;
+        if (getenv("LBCHEM_RL_SEPARATE")) h->V2.rlInMatrix = 0;
     }
     h->dacProg[7] = n_init;
     for (int i = 0; i < 8; ++i) h->dacProg[8 + i] = i < n_init ? init_species[i] : 0;

@@ -77,7 +77,10 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oMSK = p; c.oRL = p;
     if (M.dac) {                              // DAC only (the reduced instantiation of the kernel):
         p += (M.nR + 63) / 64 + 1;            //   disabled-reaction bits (by packed position), then the active-species word
-        c.oRL = p; p += 1 + (M.nR + 3) / 4;   //   int count + 16-bit list of the packed positions of the ENABLED reactions
+        //   int count + 16-bit list of the packed positions of the ENABLED reactions: its own block, or (rlInMatrix) the
+        //   tail of the matrix region -- a reduced matrix never reaches it, and when NO species was removed there is no
+        //   list (count -1 = every reaction, identity order). That is what lets a seventh reduced cell fit per SM.
+        c.oRL = p; if (!M.rlInMatrix) p += 1 + (M.nR + 3) / 4;
     }
     // vectors that other threads read (inputs of derivatives(), right-hand sides of lu_solve()) live here; the ones only
     // their owner thread touches (seulex: f(y0), y0, scale; Rosenbrock34: y0, dydx0, dfdx) sit in the group's global
@@ -90,6 +93,7 @@ __host__ __device__ __forceinline__ int ctx_layout(Ctx& c, const V2Mech& M) {
     c.oSTEP = p; p += N + 1;                  // int STEP[N] (pivot column of each row), then int SPOF[N] (DAC: species of a compact column)
     c.lda = (M.nSp + 1) | 1;                  // odd (GRI: 55): one column read across the 16 rows of a half-warp touches 16 distinct 8-byte banks
     c.oA = p; p += (M.nSp * c.lda > 2 * M.nR + M.nD) ? M.nSp * c.lda : 2 * M.nR + M.nD;   // KF/KR and the Jacobian's D terms alias the matrix
+    if (M.dac && M.rlInMatrix) c.oRL = p - (1 + (M.nR + 3) / 4);
     return (p + 1) & ~1;
 }
 #define WS(name) (base + cx->o##name)
@@ -257,9 +261,11 @@ static __device__ __noinline__ void reaction_sweep(const Ctx* cx, double* base, 
 #define RX_OFF(p) (dac && ((MSK[(p) >> 6] >> ((p) & 63)) & 1ull))
     // DAC: the sweep walks the compacted list of enabled reactions (half of GRI is typically switched off: three rounds
     // of 64 instead of six); OM of a disabled reaction was zeroed once by dac_reduce and is never touched again
-    const int nLoop = dac ? reinterpret_cast<const int*>(WS(RL))[0] : nR;
+    const int nList = dac ? reinterpret_cast<const int*>(WS(XS))[0] : -1;        // -1: every reaction, identity order (the count sits in the
+                                                                                  // queue-ticket slot, free once the cell is fetched: the list itself may share the matrix tail)
+    const int nLoop = nList < 0 ? nR : nList;
     const unsigned short* RL = reinterpret_cast<const unsigned short*>(WS(RL) + 1);
-#define RX_AT(q) (dac ? (int)RL[q] : (q))
+#define RX_AT(q) ((dac && nList >= 0) ? (int)RL[q] : (q))
     // (1) OM[p] = exp(beta ln T - Ta/T) (1 when the reaction has no such factor)
     // beta and Ta stream from global memory (L2): the next round's pair is in flight while this round's exp() runs; the
     // fall-off parameters of pass (2) are fetched here as well, ahead of their use
@@ -926,11 +932,7 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
     const int nW = (nR + 63) >> 6;
     g.sync();
     if (t <= nW) MSK[t] = 0ull;                       // every reaction takes part in the rate evaluation
-    {
-        unsigned short* RLw = reinterpret_cast<unsigned short*>(WS(RL) + 1);
-        for (int p = t; p < nR; p += TPC) RLw[p] = (unsigned short)p;
-        if (t == 0) reinterpret_cast<int*>(WS(RL))[0] = nR;
-    }
+    if (t == 0) reinterpret_cast<int*>(WS(XS))[0] = -1;      // no list: the sweep below visits every reaction
     const double T = y[nSp];
     const double lnT = log(T), invT = 1.0 / T;
     prepare(g, cx, base, y, T, lnT, true);
@@ -1058,7 +1060,9 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
     }
     g.sync();
     // compacted list of the enabled reactions, ascending packed position: thread c lists the reactions of mask word c
-    if (t < nW) {
+    if (__popcll(act) == nSp) {
+        if (t == 0) reinterpret_cast<int*>(WS(XS))[0] = -1;  // nothing removed: every reaction stays, no list (the full matrix owns the tail)
+    } else if (t < nW) {
         int basep = 0;
         for (int c = 0; c < t; ++c) { const int hiBit = nR - c * 64 < 64 ? nR - c * 64 : 64; basep += hiBit - __popcll(MSK[c]); }
         const int lim = nR - t * 64 < 64 ? nR - t * 64 : 64;
@@ -1066,7 +1070,7 @@ static __device__ __noinline__ int dac_reduce(const Ctx* cx, double* base, const
         if (lim < 64) en &= (1ull << lim) - 1ull;
         unsigned short* RLw = reinterpret_cast<unsigned short*>(WS(RL) + 1);
         while (en) { const int bpos = __ffsll((long long)en) - 1; en &= en - 1ull; RLw[basep++] = (unsigned short)(t * 64 + bpos); }
-        if (t == nW - 1) reinterpret_cast<int*>(WS(RL))[0] = basep;
+        if (t == nW - 1) reinterpret_cast<int*>(WS(XS))[0] = basep;
     }
     g.sync();
     return __popcll(act);

@@ -49,6 +49,7 @@ struct V2Mech {
     int tpc;                             // threads per cell of the compact-code kernel: 8, 16, 32 or 64 (>= nEqn)
     int tbRows;                          // rows of the seulex extrapolation table held per cell
     int wsDoubles;                       // per-cell workspace in doubles
+    int rlInMatrix;                      // DAC: the enabled-reaction list lives in the tail of the matrix region (set by lbchem_set_reduction)
 };
 
 // D term (64 bits): [0,16) index into KFR (2*pos + side)   [16,24) [24,32) [32,40) species factors (nSp = the constant 1)
