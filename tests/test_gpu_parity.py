@@ -178,6 +178,28 @@ def test_pivoting_rules(gri, flame, solver, rel_tol):
     assert eR < RTOL and (dac[0]["status"] == dac[1]["status"]).all()
 
 
+@pytest.mark.parametrize("workload", ["h2_air", "ch4_mixing_line"])
+def test_pivoting_rules_on_sub_warp_groups(workload):
+    """The same three rules where several cells share one warp (16 threads per cell for H2/O2, 8 for the 1-step CH4
+    mechanism): rule 0 against the oracle, the fallback of rule 1 bit-identical to rule 0, rule 1 within 1e-6 of rule 0."""
+    from loadbalancedchemistrymodel_b200 import workloads as W
+    mech, Y, T, p, rho = getattr(W, workload)(2000)
+    out = {}
+    for piv in (0, 1, 2):
+        opts = capi.default_options(solver="Rosenbrock34", abs_tol=1e-12, rel_tol=1e-2, pivoting=piv)
+        chem = capi.Chemistry(mech, opts)
+        out[piv] = chem.solve_host(Y, T, p, rho, DT, DTCHEM)
+        chem.close()
+    ref = O.OracleModel(mech, capi.default_options(solver="Rosenbrock34", abs_tol=1e-12, rel_tol=1e-2)).solve_batch(Y, T, p, rho, DT, DTCHEM, nthreads=8)
+    _compare(mech, Y, rho, out[0], ref, DT, f"{workload}/pivoting=0")
+    for k in ("RR", "T", "deltaTChem", "cost", "status"):
+        assert np.array_equal(out[0][k], out[2][k]), f"fallback differs from rule 0 in {k}"
+    W_ = mech.W[:, None]
+    eR = (np.abs(out[0]["RR"] - out[1]["RR"]) / (np.abs(out[0]["RR"]) + 1e-12 * W_ / DT)).max()
+    print(f"{workload}: pivoting 1 vs 0: RR {eR:.2e}")
+    assert eR < RTOL and (out[0]["status"] == out[1]["status"]).all()
+
+
 # ---- the other BASELINE configurations (parity-test cases, not bench lines) -------------------------
 def _solve_both(mech, Y, T, p, rho, opts, dt=DT, dtchem=DTCHEM):
     chem = capi.Chemistry(mech, opts)
